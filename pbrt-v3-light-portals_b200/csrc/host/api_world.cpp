@@ -1,0 +1,297 @@
+// SceneApi, world-block part: materials, lights, shapes, WorldEnd.
+// References: MakeMaterial api.cpp:548-620, TextureParams (core/paramset.cpp:
+// 690-800), MakeLight/MakeAreaLight api.cpp:742-785, pbrtShape api.cpp:1348-1436,
+// CreateAAPortal lights/portal_arealight.cpp:245-300.
+#include <cmath>
+#include <cstring>
+
+#include "api.h"
+#include "xform.h"
+
+namespace pg {
+
+namespace {
+
+// TextureParams lookups restricted to constant textures: a "texture" parameter
+// naming a constant texture, else the material/shape value, shape overriding
+// material (paramset.cpp: GetSpectrumTexture / GetFloatTexture / FindFloat).
+struct TexParams {
+    const ParamSet &geom, &mat;
+    const std::map<std::string, float> &ftex;
+    const std::map<std::string, RGB> &stex;
+    RGB spectrum(const std::string &n, RGB def) const {
+        std::string name = geom.findTexture(n);
+        if (name.empty()) name = mat.findTexture(n);
+        if (!name.empty()) {
+            auto it = stex.find(name);
+            if (it != stex.end()) return it->second;
+            hostError("Couldn't find spectrum texture named \"%s\" for parameter \"%s\"", name.c_str(), n.c_str());
+        }
+        RGB val = mat.findOneSpectrum(n, def);
+        return geom.findOneSpectrum(n, val);
+    }
+    float scalar(const std::string &n, float def) const {
+        std::string name = geom.findTexture(n);
+        if (name.empty()) name = mat.findTexture(n);
+        if (!name.empty()) {
+            auto it = ftex.find(name);
+            if (it != ftex.end()) return it->second;
+            hostError("Couldn't find float texture named \"%s\" for parameter \"%s\"", name.c_str(), n.c_str());
+        }
+        float val = mat.findOneFloat(n, def);
+        return geom.findOneFloat(n, val);
+    }
+    bool has(const std::string &n) const {  // GetFloatTextureOrNull != nullptr
+        if (!geom.findTexture(n).empty() || !mat.findTexture(n).empty()) return true;
+        return geom.find(n, ParamType::Float) || mat.find(n, ParamType::Float);
+    }
+    bool boolean(const std::string &n, bool def) const { return geom.findOneBool(n, mat.findOneBool(n, def)); }
+};
+
+// TrowbridgeReitzDistribution::RoughnessToAlpha, core/microfacet.h:126-132.
+// The reference evaluates this per hit; with constant textures the value is
+// the same every time, so it is folded here with the same libm call.
+float roughnessToAlpha(float roughness) {
+    roughness = std::max(roughness, (float)1e-3);
+    float x = std::log(roughness);
+    return 1.62142f + 0.819955f * x + 0.1734f * x * x + 0.0171201f * x * x * x + 0.000640711f * x * x * x * x;
+}
+
+void put3(float *dst, const RGB &c) { dst[0] = c[0], dst[1] = c[1], dst[2] = c[2]; }
+
+}  // namespace
+
+int SceneApi::makeMaterial(const std::string &name, const ParamSet &shapeParams, const ParamSet &matParams) {
+    if (name.empty() || name == "none") return -1;
+    TexParams mp{shapeParams, matParams, gs.floatTextures, gs.spectrumTextures};
+    MaterialData m;
+    if (mp.has("bumpmap")) hostWarning("bump mapping is not supported by the GPU path integrator; ignored");
+    if (name == "plastic") {  // materials/plastic.cpp:45-85
+        m.tag = PBRTGPU_MAT_PLASTIC;
+        put3(m.params + 0, mp.spectrum("Kd", RGB(0.25f)).clamp());
+        put3(m.params + 3, mp.spectrum("Ks", RGB(0.25f)).clamp());
+        float rough = mp.scalar("roughness", .1f);
+        if (mp.boolean("remaproughness", true)) rough = roughnessToAlpha(rough);
+        m.params[6] = rough;
+    } else if (name == "glass") {  // materials/glass.cpp:45-113
+        m.tag = PBRTGPU_MAT_GLASS;
+        put3(m.params + 0, mp.spectrum("Kr", RGB(1.f)).clamp());
+        put3(m.params + 3, mp.spectrum("Kt", RGB(1.f)).clamp());
+        float eta = mp.has("eta") ? mp.scalar("eta", 1.5f) : mp.scalar("index", 1.5f);
+        float ur = mp.scalar("uroughness", 0.f), vr = mp.scalar("vroughness", 0.f);
+        bool remap = mp.boolean("remaproughness", true);
+        bool isSpecular = ur == 0 && vr == 0;
+        if (!isSpecular && remap) ur = roughnessToAlpha(ur), vr = roughnessToAlpha(vr);
+        m.params[6] = ur, m.params[7] = vr, m.params[8] = eta, m.params[9] = isSpecular ? 1.f : 0.f;
+    } else if (name == "dispersive_glass") {  // materials/dispersive_glass.cpp:48-145
+        m.tag = PBRTGPU_MAT_DISPERSIVE_GLASS;
+        put3(m.params + 0, mp.spectrum("Kr", RGB(1.f)).clamp());
+        put3(m.params + 3, mp.spectrum("Kt", RGB(1.f)).clamp());
+        float etaMin = mp.has("etaMin") ? mp.scalar("etaMin", 1.5f) : mp.scalar("indexMin", 1.5f);
+        float etaMax = mp.has("etaMax") ? mp.scalar("etaMax", 1.5f) : mp.scalar("indexMax", 1.5f);
+        float ur = mp.scalar("uroughness", 0.f), vr = mp.scalar("vroughness", 0.f);
+        bool remap = mp.boolean("remaproughness", false);
+        bool isSpecular = ur == 0 && vr == 0;
+        // path uses bsdf[0] only, for which the remap has been applied once (dispersive_glass.cpp:98-101)
+        if (!isSpecular && remap) ur = roughnessToAlpha(ur), vr = roughnessToAlpha(vr);
+        // Cauchy coefficients (dispersive_glass.cpp:44-45, 63-65); lambda in nm
+        const float lambdaMinSq = 400 * 400, lambdaMaxSq = 700 * 700;
+        const float cauchyB = (lambdaMinSq * etaMax - lambdaMaxSq * etaMin) / (lambdaMinSq - lambdaMaxSq);
+        const float cauchyC = lambdaMinSq * (etaMax - cauchyB);
+        m.params[6] = ur, m.params[7] = vr, m.params[8] = cauchyB, m.params[9] = isSpecular ? 1.f : 0.f;
+        m.params[10] = cauchyC, m.params[11] = etaMin, m.params[12] = etaMax;
+    } else if (name == "mirror") {  // materials/mirror.cpp:45-64
+        m.tag = PBRTGPU_MAT_MIRROR;
+        put3(m.params + 0, mp.spectrum("Kr", RGB(0.9f)).clamp());
+    } else {
+        if (name != "matte") hostWarning("Material \"%s\" is not supported by the GPU path integrator. Using \"matte\".", name.c_str());
+        m.tag = PBRTGPU_MAT_MATTE;  // materials/matte.cpp:45-73
+        put3(m.params + 0, mp.spectrum("Kd", RGB(0.5f)).clamp());
+        m.params[3] = clampf(mp.scalar("sigma", 0.f), 0, 90);
+    }
+    for (size_t i = 0; i < sc->materials.size(); ++i)
+        if (sc->materials[i].tag == m.tag && !memcmp(sc->materials[i].params, m.params, sizeof(m.params))) return (int)i;
+    sc->materials.push_back(m);
+    return (int)sc->materials.size() - 1;
+}
+
+int SceneApi::materialForShape(const ParamSet &shapeParams) {  // GraphicsState::GetMaterialForShape
+    return makeMaterial(gs.material.name, shapeParams, gs.material.params);
+}
+
+void SceneApi::LightSource(const std::string &name, const ParamSet &params) {
+    if (state == State::Options) {
+        hostError("Scene description must be inside world block; \"LightSource\" not allowed. Ignoring.");
+        return;
+    }
+    LightData l;
+    if (name == "infinite" || name == "exinfinite") {  // lights/infinite.cpp:176-186
+        RGB L = params.findOneSpectrum("L", RGB(1.f)), s = params.findOneSpectrum("scale", RGB(1.f));
+        std::string texmap = params.findOneString("mapname", "");
+        params.findOneInt("samples", params.findOneInt("nsamples", 1));
+        if (!texmap.empty()) {
+            hostError("LightSource \"infinite\": environment maps (\"mapname\") are not supported by the GPU path integrator");
+            failed = true;
+            return;
+        }
+        l.tag = PBRTGPU_LIGHT_INFINITE;
+        put3(l.params, L * s);
+        memcpy(l.params + 8, &ctm.m.m[0][0], 16 * sizeof(float));      // LightToWorld
+        memcpy(l.params + 24, &ctm.mInv.m[0][0], 16 * sizeof(float));  // WorldToLight
+    } else if (name == "point") {  // lights/point.cpp:80-88
+        RGB I = params.findOneSpectrum("I", RGB(1.f)), s = params.findOneSpectrum("scale", RGB(1.f));
+        V3 P = params.findOnePoint3("from", v3(0, 0, 0));
+        Xform l2w = xfMul(xfTranslate(P), ctm);
+        V3 pLight = xformPoint(l2w.m, v3(0, 0, 0));
+        l.tag = PBRTGPU_LIGHT_POINT;
+        put3(l.params, I * s);
+        l.params[3] = pLight.x, l.params[4] = pLight.y, l.params[5] = pLight.z;
+    } else if (name == "distant") {  // lights/distant.cpp
+        RGB L = params.findOneSpectrum("L", RGB(1.f)), s = params.findOneSpectrum("scale", RGB(1.f));
+        V3 from = params.findOnePoint3("from", v3(0, 0, 0)), to = params.findOnePoint3("to", v3(0, 0, 1));
+        V3 dir = from - to;
+        V3 w = normalize(xformVector(ctm.m, dir));
+        l.tag = PBRTGPU_LIGHT_DISTANT;
+        put3(l.params, L * s);
+        l.params[3] = w.x, l.params[4] = w.y, l.params[5] = w.z;
+    } else {
+        hostError("LightSource: light type \"%s\" is not supported by the GPU path integrator.", name.c_str());
+        failed = true;
+        return;
+    }
+    params.reportUnused();
+    sc->lights.push_back(l);
+}
+
+// "((AA lox loy loz hix hiy hiz axis +|-) ...)" -> portals.  The reference
+// hands the string to sexpresso and reads child(0)'s children
+// (portal_arealight.cpp:256-279); tokens are whitespace/parenthesis separated.
+static std::vector<PortalData> parsePortalData(const std::string &s, const PlaneData &lightShape) {
+    std::vector<PortalData> out;
+    std::vector<std::string> tok;
+    std::string cur;
+    for (char c : s) {
+        if (c == '(' || c == ')' || c == ' ' || c == '\t' || c == '\n') {
+            if (!cur.empty()) tok.push_back(cur), cur.clear();
+            if (c == '(' || c == ')') tok.push_back(std::string(1, c));
+        } else
+            cur.push_back(c);
+    }
+    if (!cur.empty()) tok.push_back(cur);
+    int depth = 0;
+    for (size_t i = 0; i < tok.size(); ++i) {
+        if (tok[i] == "(") {
+            ++depth;
+            if (depth == 2 && i + 9 < tok.size() && tok[i + 1] == "AA") {
+                PortalData p;
+                p.lo = v3(std::stof(tok[i + 2]), std::stof(tok[i + 3]), std::stof(tok[i + 4]));
+                p.hi = v3(std::stof(tok[i + 5]), std::stof(tok[i + 6]), std::stof(tok[i + 7]));
+                p.ax = std::stoi(tok[i + 8]);
+                p.facingFw = tok[i + 9] == "+";
+                // AAPortal builds its plane with the LIGHT's transforms (aaportal.cpp:12)
+                int ax0 = p.ax == 2 ? 0 : (p.ax == 0 ? 1 : 2), ax1 = p.ax == 2 ? 1 : (p.ax == 0 ? 2 : 0);
+                V3 loW = xformPoint(lightShape.o2w.m, p.lo), hiW = xformPoint(lightShape.o2w.m, p.hi);
+                p.area = (hiW[ax0] - loW[ax0]) * (hiW[ax1] - loW[ax1]);
+                out.push_back(p);
+            }
+        } else if (tok[i] == ")")
+            --depth;
+    }
+    return out;
+}
+
+static float shapeArea(const SceneDesc &sc, const PrimDesc &p) {
+    if (p.type == PBRTGPU_PRIM_TRIANGLE) {  // Triangle::Area, triangle.cpp:576-582
+        const MeshData &m = sc.meshes[p.shape];
+        V3 p0 = m.p[m.indices[3 * p.tri]], p1 = m.p[m.indices[3 * p.tri + 1]], p2 = m.p[m.indices[3 * p.tri + 2]];
+        return 0.5 * length(cross(p1 - p0, p2 - p0));
+    }
+    if (p.type == PBRTGPU_PRIM_SPHERE) {  // Sphere::Area, sphere.cpp:217
+        const SphereData &s = sc.spheres[p.shape];
+        return s.phiMax * s.radius * (s.zMax - s.zMin);
+    }
+    return sc.planes[p.shape].area;
+}
+
+void SceneApi::Shape(const std::string &name, const ParamSet &params) {
+    if (state == State::Options) {
+        hostError("Scene description must be inside world block; \"Shape\" not allowed. Ignoring.");
+        return;
+    }
+    if (inObject) return;
+    ShapeResult sr;
+    if (!makeShape(*sc, name, ctm, gs.reverseOrientation, params, &sr)) {
+        failed = true;
+        return;
+    }
+    int mtl = materialForShape(params);
+    params.reportUnused();
+    for (int i = 0; i < sr.count; ++i) {
+        PrimDesc p;
+        p.type = (uint8_t)sr.type;
+        p.shape = sr.mesh;
+        p.tri = i;
+        p.material = mtl;
+        if (!gs.areaLight.empty()) {
+            const ParamSet &lp = gs.areaLightParams;
+            LightData l;
+            RGB L = lp.findOneSpectrum("L", RGB(1.f)), s = lp.findOneSpectrum("scale", RGB(1.f));
+            lp.findOneInt("samples", lp.findOneInt("nsamples", 1));
+            bool twoSided = lp.findOneBool("twosided", false);
+            bool made = true;
+            if (gs.areaLight == "area" || gs.areaLight == "diffuse") {
+                l.tag = PBRTGPU_LIGHT_DIFFUSE_AREA;
+            } else if (gs.areaLight == "portal") {
+                if (sr.type != PBRTGPU_PRIM_AAPLANE) {
+                    // the reference dereferences a null AAPlaneShape here (api.cpp:778-779)
+                    hostError("AreaLightSource \"portal\" requires Shape \"aaplane\"");
+                    failed = true;
+                    return;
+                }
+                l.tag = PBRTGPU_LIGHT_PORTAL_AREA;
+                l.portals = parsePortalData(lp.findOneString("portalData", ""), sc->planes[sr.mesh]);
+                std::string st = lp.findOneString("strategy", "light");
+                if (st == "light") l.strategy = PBRTGPU_PORTAL_UNIFORM_LIGHT;
+                else if (st == "portal") l.strategy = PBRTGPU_PORTAL_UNIFORM_PORTAL;
+                else if (st == "projection") l.strategy = PBRTGPU_PORTAL_PROJECTION;
+                else {
+                    hostWarning("AAPortal strategy unknown");
+                    l.strategy = PBRTGPU_PORTAL_UNIFORM_LIGHT;  // the reference leaves it uninitialised
+                }
+            } else {
+                hostWarning("Area light \"%s\" unknown.", gs.areaLight.c_str());
+                made = false;
+            }
+            if (made) {
+                put3(l.params, L * s);
+                l.params[3] = twoSided ? 1.f : 0.f;
+                l.params[4] = shapeArea(*sc, p);
+                l.prim = (int)sc->prims.size();
+                p.light = (int)sc->lights.size();
+                sc->lights.push_back(l);
+            }
+            if (i == sr.count - 1) lp.reportUnused();
+        }
+        sc->prims.push_back(p);
+    }
+}
+
+void SceneApi::WorldEnd() {
+    if (state == State::Options) {
+        hostError("Scene description must be inside world block; \"WorldEnd\" not allowed. Ignoring.");
+        return;
+    }
+    while (!pushedStates.empty()) {
+        hostWarning("Missing end to pbrtAttributeBegin()");
+        pushedStates.pop_back();
+        pushedTransforms.pop_back();
+    }
+    while (!pushedTransforms.empty()) {
+        hostWarning("Missing end to pbrtTransformBegin()");
+        pushedTransforms.pop_back();
+    }
+    sc->worldEnded = true;
+    state = State::Options;
+}
+
+}  // namespace pg

@@ -1,0 +1,99 @@
+// Device context behind the opaque pbrtgpu_ctx handle.
+#ifndef PG_DEVICE_CTX_H
+#define PG_DEVICE_CTX_H
+
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdio>
+#include <string>
+#include <vector>
+
+#include "../../../include/pbrtgpu.h"
+#include "bvh.h"
+
+namespace pg {
+
+// Everything a kernel needs to know about the scene; passed by value.
+struct DevScene {
+    DevBVH bvh;
+    int nPrims, nLights, nMaterials;
+    const int *primOrigId;
+    const int *primMaterial;
+    const int *primLight;
+    const unsigned char *primFlags;
+    const float *triN;   // 9 per slot or null
+    const float *triUV;  // 6 per slot or null
+    const float *triS;   // 9 per slot or null
+    const int *matTag;
+    const float *matParams;
+    const int *lightTag;
+    const int *lightPrim;
+    const int *lightStrategy;
+    const int *lightPortalBegin;
+    const float *lightParams;
+    const float *portalParams;
+    const float *lightCdf;  // nLights+1 (power strategy) or null
+    float lightFuncInt;
+    const float *lightFunc;
+    float worldCenter[3], worldRadius;
+};
+
+struct DeviceBuffer {
+    void *p = nullptr;
+    size_t bytes = 0;
+};
+
+}  // namespace pg
+
+struct pbrtgpu_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    bool ownStream = false;
+    std::string lastError;
+    bool haveScene = false;
+    pg::DevScene scene;
+    std::vector<void *> sceneAllocs;  // freed on re-upload / destroy
+    // Halton tables (uploaded at create)
+    unsigned short *dPerms = nullptr;
+    // render scratch, grown on demand
+    pg::DeviceBuffer scratch[16];
+    pg::DeviceBuffer film;
+    int smCount = 148;
+    long long launches = 0;
+
+    int fail(int code, const char *fmt, ...) {
+        char buf[1024];
+        va_list ap;
+        va_start(ap, fmt);
+        vsnprintf(buf, sizeof(buf), fmt, ap);
+        va_end(ap);
+        lastError = buf;
+        return code;
+    }
+};
+
+#define PG_CUDA(ctx, call)                                                                              \
+    do {                                                                                                \
+        cudaError_t e_ = (call);                                                                        \
+        if (e_ != cudaSuccess)                                                                          \
+            return (ctx)->fail(PBRTGPU_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), \
+                               __FILE__, __LINE__);                                                     \
+    } while (0)
+
+namespace pg {
+int ensureBuffer(pbrtgpu_ctx *ctx, DeviceBuffer &b, size_t bytes);
+template <typename T>
+int uploadArray(pbrtgpu_ctx *ctx, const T *host, size_t count, const T **dev) {
+    *dev = nullptr;
+    if (!host || count == 0) return PBRTGPU_OK;
+    void *d = nullptr;
+    PG_CUDA(ctx, cudaMalloc(&d, count * sizeof(T)));
+    ctx->sceneAllocs.push_back(d);
+    PG_CUDA(ctx, cudaMemcpyAsync(d, host, count * sizeof(T), cudaMemcpyHostToDevice, ctx->stream));
+    *dev = (const T *)d;
+    return PBRTGPU_OK;
+}
+}  // namespace pg
+
+#endif

@@ -1,0 +1,151 @@
+// Context lifetime and scene upload: reference-layout arrays (pbrtgpu_scene)
+// -> device layout (bvh.h).  Host code only; no kernels here.
+#include <cstring>
+#include <vector>
+
+#include "../common/halton_tables.h"
+#include "ctx.h"
+#include "layout_build.h"
+
+using namespace pg;
+
+static std::string gCreateError;
+
+namespace pg {
+int ensureBuffer(pbrtgpu_ctx *ctx, DeviceBuffer &b, size_t bytes) {
+    if (b.bytes >= bytes) return PBRTGPU_OK;
+    if (b.p) PG_CUDA(ctx, cudaFree(b.p));
+    b.p = nullptr;
+    b.bytes = 0;
+    PG_CUDA(ctx, cudaMalloc(&b.p, bytes));
+    b.bytes = bytes;
+    return PBRTGPU_OK;
+}
+}  // namespace pg
+
+static void freeScene(pbrtgpu_ctx *ctx) {
+    for (void *p : ctx->sceneAllocs) cudaFree(p);
+    ctx->sceneAllocs.clear();
+    ctx->haveScene = false;
+}
+
+extern "C" {
+
+int pbrtgpu_abi_version(void) { return PBRTGPU_ABI_VERSION; }
+
+const char *pbrtgpu_last_error(const pbrtgpu_ctx *ctx) { return ctx ? ctx->lastError.c_str() : gCreateError.c_str(); }
+
+int pbrtgpu_create(int cuda_device, pbrtgpu_ctx **out) {
+    if (!out) return PBRTGPU_ERR_INVALID;
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0) {
+        gCreateError = std::string("no CUDA device available: ") + (e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0") +
+                       " (libpbrtgpu has no CPU fallback)";
+        return PBRTGPU_ERR_NO_DEVICE;
+    }
+    if (cuda_device < 0 || cuda_device >= count) {
+        gCreateError = "cuda_device out of range";
+        return PBRTGPU_ERR_INVALID;
+    }
+    pbrtgpu_ctx *ctx = new pbrtgpu_ctx;
+    ctx->device = cuda_device;
+    auto bail = [&](cudaError_t err, const char *what) {
+        gCreateError = std::string(what) + ": " + cudaGetErrorString(err);
+        delete ctx;
+        return PBRTGPU_ERR_CUDA;
+    };
+    if ((e = cudaSetDevice(cuda_device)) != cudaSuccess) return bail(e, "cudaSetDevice");
+    if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "cudaStreamCreate");
+    ctx->ownStream = true;
+    cudaDeviceGetAttribute(&ctx->smCount, cudaDevAttrMultiProcessorCount, cuda_device);
+    // Halton digit permutations (7.4 MB of uint16), generated, not stored
+    std::vector<uint16_t> perms = radicalInversePermutations(firstPrimes());
+    if ((e = cudaMalloc((void **)&ctx->dPerms, perms.size() * sizeof(uint16_t))) != cudaSuccess) return bail(e, "cudaMalloc(perms)");
+    if ((e = cudaMemcpy(ctx->dPerms, perms.data(), perms.size() * sizeof(uint16_t), cudaMemcpyHostToDevice)) != cudaSuccess)
+        return bail(e, "cudaMemcpy(perms)");
+    *out = ctx;
+    return PBRTGPU_OK;
+}
+
+void pbrtgpu_destroy(pbrtgpu_ctx *ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    freeScene(ctx);
+    for (auto &b : ctx->scratch)
+        if (b.p) cudaFree(b.p);
+    if (ctx->film.p) cudaFree(ctx->film.p);
+    if (ctx->dPerms) cudaFree(ctx->dPerms);
+    if (ctx->ownStream && ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+int pbrtgpu_set_stream(pbrtgpu_ctx *ctx, void *cuda_stream) {
+    if (!ctx) return PBRTGPU_ERR_INVALID;
+    if (ctx->ownStream && ctx->stream) cudaStreamDestroy(ctx->stream);
+    ctx->stream = (cudaStream_t)cuda_stream;
+    ctx->ownStream = false;
+    return PBRTGPU_OK;
+}
+
+int pbrtgpu_upload_scene(pbrtgpu_ctx *ctx, const pbrtgpu_scene *s) {
+    if (!ctx || !s) return PBRTGPU_ERR_INVALID;
+    PG_CUDA(ctx, cudaSetDevice(ctx->device));
+    if (s->n_nodes <= 0 || s->n_prims <= 0) return ctx->fail(PBRTGPU_ERR_INVALID, "scene has no primitives");
+    if (!s->bvh_bounds || !s->bvh_offset || !s->bvh_nprims || !s->bvh_axis || !s->prim_type || !s->tri_p || !s->prim_orig_id)
+        return ctx->fail(PBRTGPU_ERR_INVALID, "scene arrays missing");
+    // validate tree shape so that traversal cannot run away on bad input
+    for (int i = 0; i < s->n_nodes; ++i) {
+        if (s->bvh_nprims[i] == 0) {
+            if (i + 1 >= s->n_nodes || s->bvh_offset[i] <= i || s->bvh_offset[i] >= s->n_nodes || s->bvh_axis[i] > 2)
+                return ctx->fail(PBRTGPU_ERR_INVALID, "BVH node %d: bad child offset / axis", i);
+        } else if (s->bvh_offset[i] < 0 || s->bvh_offset[i] + (int)s->bvh_nprims[i] > s->n_prims)
+            return ctx->fail(PBRTGPU_ERR_INVALID, "BVH leaf %d: primitive range out of bounds", i);
+    }
+    freeScene(ctx);
+    DevScene &d = ctx->scene;
+    memset(&d, 0, sizeof(d));
+
+    std::vector<F4> wide;
+    buildWideNodes(s, &wide);
+    std::vector<F4> tris;
+    {
+        std::string err;
+        if (!buildTris(s, &tris, &err)) return ctx->fail(PBRTGPU_ERR_INVALID, "%s", err.c_str());
+    }
+
+    int rc;
+#define UP(host, count, dev) \
+    if ((rc = uploadArray(ctx, host, (size_t)(count), dev)) != PBRTGPU_OK) return rc;
+    UP(wide.data(), wide.size(), &d.bvh.nodes);
+    UP(tris.data(), tris.size(), &d.bvh.tris);
+    UP(s->plane_params, (size_t)s->n_planes * PBRTGPU_PLANE_STRIDE, &d.bvh.planeParams);
+    UP(s->sphere_params, (size_t)s->n_spheres * PBRTGPU_SPHERE_STRIDE, &d.bvh.sphereParams);
+    d.nPrims = s->n_prims;
+    d.nLights = s->n_lights;
+    d.nMaterials = s->n_materials;
+    UP(s->prim_orig_id, s->n_prims, &d.primOrigId);
+    UP(s->prim_material, s->prim_material ? s->n_prims : 0, &d.primMaterial);
+    UP(s->prim_light, s->prim_light ? s->n_prims : 0, &d.primLight);
+    UP(s->prim_flags, s->prim_flags ? s->n_prims : 0, &d.primFlags);
+    UP(s->tri_n, s->tri_n ? 9 * (size_t)s->n_prims : 0, &d.triN);
+    UP(s->tri_uv, s->tri_uv ? 6 * (size_t)s->n_prims : 0, &d.triUV);
+    UP(s->tri_s, s->tri_s ? 9 * (size_t)s->n_prims : 0, &d.triS);
+    UP(s->mat_tag, s->n_materials, &d.matTag);
+    UP(s->mat_params, (size_t)s->n_materials * PBRTGPU_MAT_STRIDE, &d.matParams);
+    UP(s->light_tag, s->n_lights, &d.lightTag);
+    UP(s->light_prim, s->n_lights, &d.lightPrim);
+    UP(s->light_strategy, s->n_lights, &d.lightStrategy);
+    UP(s->light_portal_begin, s->light_portal_begin ? s->n_lights + 1 : 0, &d.lightPortalBegin);
+    UP(s->light_params, (size_t)s->n_lights * PBRTGPU_LIGHT_STRIDE, &d.lightParams);
+    UP(s->portal_params, (size_t)s->n_portals * PBRTGPU_PORTAL_STRIDE, &d.portalParams);
+#undef UP
+    memcpy(d.worldCenter, s->world_center, sizeof(d.worldCenter));
+    d.worldRadius = s->world_radius;
+    PG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->haveScene = true;
+    return PBRTGPU_OK;
+}
+
+}  // extern "C"

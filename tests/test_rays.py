@@ -1,0 +1,159 @@
+"""Tier-1 parity: BVHAccel::Intersect / IntersectP (accelerators/bvh.cpp:662-738).
+
+CPU (`-m "not gpu"`):
+  * the host front end reproduces the reference's BVH and primitive table bit for bit
+    (golden dump from oracle/_ref/ref_harness),
+  * the oracle restatement reproduces the reference's hit IDs, t and occlusion bits,
+  * the device traversal code, stepped on the CPU, does too.
+GPU (`-m gpu`): the CUDA kernels, through the C ABI, against the golden vectors
+(bit-exact IDs, t and occlusion) and against the oracle on larger batches.
+"""
+import hashlib
+import os
+
+import numpy as np
+import pytest
+
+import util
+from conftest import GOLDEN, scene_path
+
+SCENE = "tri_soup.pbrt"
+
+
+@pytest.fixture(scope="module")
+def soup(pkg):
+    return pkg.HostScene(scene_path(SCENE))
+
+
+@pytest.fixture(scope="module")
+def golden():
+    return np.load(os.path.join(GOLDEN, "tri_soup_rays.npz"))
+
+
+def ray_sets(view):
+    return {
+        "incoherent": util.rays_incoherent_closest(view, 40000, seed=42),
+        "toward": util.rays_toward_box(40000, [-10, -10, -10], [10, 10, 10], seed=44),
+        "edges": util.rays_edge_cases(view, 20000, seed=45),
+        "shadow": util.rays_shadow(view, 40000, seed=43),
+    }
+
+
+def test_host_bvh_matches_reference_dump(soup):
+    g = np.load(os.path.join(GOLDEN, "tri_soup_scene.npz"))
+    nodes, prims = g["nodes"], g["prims"]
+    v = soup.view
+    assert v.n_nodes == len(nodes) and v.n_prims == len(prims)
+    assert np.array_equal(util.bits(v.array("bvh_bounds", v.n_nodes, 6)), nodes[:, :24].copy().view(np.uint32))
+    assert np.array_equal(v.array("bvh_offset", v.n_nodes), nodes[:, 24:28].copy().view(np.int32).ravel())
+    nprims = nodes[:, 28:30].copy().view(np.uint16).ravel()
+    assert np.array_equal(v.array("bvh_nprims", v.n_nodes), nprims)
+    assert np.array_equal(v.array("bvh_axis", v.n_nodes)[nprims == 0], nodes[:, 30][nprims == 0])
+    assert np.array_equal(v.array("prim_orig_id", v.n_prims), prims[:, :4].copy().view(np.int32).ravel())
+    assert np.array_equal(v.array("prim_type", v.n_prims), prims[:, 4:8].copy().view(np.int32).ravel())
+    assert np.array_equal(util.bits(v.array("tri_p", v.n_prims, 9)), prims[:, 8:].copy().view(np.uint32).reshape(-1, 9))
+
+
+def test_ray_generators_are_stable(soup, golden):
+    for name, rays in ray_sets(soup.view).items():
+        assert hashlib.sha256(rays.tobytes()).hexdigest() == str(golden[name + "_sha"]), name
+
+
+@pytest.mark.parametrize("name", ["incoherent", "toward", "edges", "shadow"])
+def test_oracle_matches_reference(soup, golden, oracle_lib, name):
+    rays = ray_sets(soup.view)[name]
+    ids, t, _, (V, T) = util.oracle_closest(oracle_lib, soup.view, rays)
+    assert np.array_equal(ids, golden[name + "_id"])
+    assert np.array_equal(util.bits(t), util.bits(golden[name + "_t"]))
+    occ, _ = util.oracle_any(oracle_lib, soup.view, rays)
+    assert np.array_equal(occ, golden[name + "_occ"])
+    assert V > 0 and T > 0
+
+
+@pytest.mark.parametrize("name", ["incoherent", "toward", "edges", "shadow"])
+def test_device_traversal_logic_on_cpu(soup, golden, hostsim_lib, name):
+    rays = ray_sets(soup.view)[name]
+    ids, t, _ = util.hostsim_closest(hostsim_lib, soup.view, rays)
+    assert np.array_equal(ids, golden[name + "_id"])
+    assert np.array_equal(util.bits(t), util.bits(golden[name + "_t"]))
+    assert np.array_equal(util.hostsim_any(hostsim_lib, soup.view, rays), golden[name + "_occ"])
+
+
+def test_oracle_against_live_reference(pkg, oracle_lib, ref_harness, tmp_path):
+    """Where oracle/_ref is present, also pin the oracle on the staged killeroo scene."""
+    import subprocess
+    if ref_harness is None:
+        pytest.skip("oracle/_ref not built")
+    path = scene_path("killeroo-path.pbrt")
+    hs = pkg.HostScene(path)
+    rays = np.concatenate([util.rays_incoherent_closest(hs.view, 100000, seed=1),
+                           util.rays_toward_box(100000, [-100, -100, -150], [100, 150, 50], seed=2)])
+    rp = str(tmp_path / "r.bin")
+    rays.tofile(rp)
+    subprocess.check_call([ref_harness, "intersect", path, rp, rp + ".c", "closest", "8"], stdout=subprocess.DEVNULL)
+    subprocess.check_call([ref_harness, "intersect", path, rp, rp + ".a", "any", "8"], stdout=subprocess.DEVNULL)
+    ref = np.fromfile(rp + ".c", dtype=np.int32).reshape(-1, 2)
+    ids, t, _, _ = util.oracle_closest(oracle_lib, hs.view, rays)
+    assert np.array_equal(ids, ref[:, 0])
+    assert np.array_equal(util.bits(t), ref[:, 1].copy().view(np.uint32))
+    occ, _ = util.oracle_any(oracle_lib, hs.view, rays)
+    assert np.array_equal(occ, np.fromfile(rp + ".a", dtype=np.uint8))
+
+
+# ---------------------------------------------------------------- GPU
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["incoherent", "toward", "edges", "shadow"])
+def test_gpu_matches_golden(soup, golden, gpu, name):
+    gpu.upload(soup)
+    rays = ray_sets(soup.view)[name]
+    ids, t, _ = gpu.intersect_closest(rays)
+    assert np.array_equal(ids, golden[name + "_id"])
+    assert np.array_equal(util.bits(t), util.bits(golden[name + "_t"]))
+    assert np.array_equal(gpu.intersect_any(rays), golden[name + "_occ"])
+
+
+@pytest.mark.gpu
+def test_gpu_matches_oracle_large(soup, gpu, oracle_lib):
+    gpu.upload(soup)
+    rays = np.concatenate([util.rays_incoherent_closest(soup.view, 1000000, seed=7),
+                           util.rays_toward_box(1000000, [-10, -10, -10], [10, 10, 10], seed=8),
+                           util.rays_edge_cases(soup.view, 300000, seed=9)])
+    ids, t, b = gpu.intersect_closest(rays)
+    oid, ot, ob, _ = util.oracle_closest(oracle_lib, soup.view, rays)
+    assert np.array_equal(ids, oid)
+    assert np.array_equal(util.bits(t), util.bits(ot))
+    assert np.array_equal(util.bits(b), util.bits(ob))
+    srays = util.rays_shadow(soup.view, 1000000, seed=10)
+    occ, _ = util.oracle_any(oracle_lib, soup.view, srays)
+    assert np.array_equal(gpu.intersect_any(srays), occ)
+
+
+@pytest.mark.gpu
+def test_gpu_killeroo_matches_oracle(pkg, gpu, oracle_lib):
+    hs = pkg.HostScene(scene_path("killeroo-path.pbrt"))
+    gpu.upload(hs)
+    rays = np.concatenate([util.rays_incoherent_closest(hs.view, 1000000, seed=1),
+                           util.rays_toward_box(2000000, [-100, -100, -150], [100, 150, 50], seed=2)])
+    ids, t, _ = gpu.intersect_closest(rays)
+    oid, ot, _, _ = util.oracle_closest(oracle_lib, hs.view, rays)
+    assert np.array_equal(ids, oid)
+    assert np.array_equal(util.bits(t), util.bits(ot))
+    srays = util.rays_shadow(hs.view, 1000000, seed=3, lo=np.array([-150., -150, -150]), hi=np.array([250., 250, 100]))
+    occ, _ = util.oracle_any(oracle_lib, hs.view, srays)
+    assert np.array_equal(gpu.intersect_any(srays), occ)
+
+
+@pytest.mark.gpu
+def test_gpu_edge_inputs(soup, gpu):
+    gpu.upload(soup)
+    ids, t, _ = gpu.intersect_closest(np.zeros((0, 8), np.float32))
+    assert len(ids) == 0
+    # zero direction, NaN origin, negative tMax: must terminate and report a miss
+    bad = np.zeros((3, 8), np.float32)
+    bad[0, 3] = np.inf
+    bad[1, :3] = np.nan; bad[1, 3] = np.inf; bad[1, 4:7] = [0, 0, 1]
+    bad[2, 3] = -1; bad[2, 4:7] = [0, 1, 0]
+    ids, t, _ = gpu.intersect_closest(bad)
+    assert (ids == -1).all()
+    assert (gpu.intersect_any(bad) == 0).all()

@@ -23,6 +23,13 @@
 #define PG_HD_NOINLINE inline
 #endif
 
+// read-only global loads (scalar); on the host a plain dereference
+#if defined(__CUDA_ARCH__)
+#define PG_LD(p) __ldg(p)
+#else
+#define PG_LD(p) (*(p))
+#endif
+
 namespace pg {
 
 constexpr float kInfinity = INFINITY;
@@ -76,6 +83,7 @@ PG_HD float nextFloatDown(float v) {
     return bitsToFloat(ui);
 }
 
+PG_HD bool isInfF(float v) { return v == kInfinity || v == -kInfinity; }
 PG_HD float clampf(float v, float lo, float hi) {
     return v < lo ? lo : (v > hi ? hi : v);
 }

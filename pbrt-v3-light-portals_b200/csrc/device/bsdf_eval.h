@@ -1,0 +1,315 @@
+// Second half of bsdf.h: per-lobe f / Pdf / Sample_f and the BSDF container.
+#ifndef PG_DEVICE_BSDF_EVAL_H
+#define PG_DEVICE_BSDF_EVAL_H
+
+namespace pg {
+
+PG_HD bool lobeMatches(const Lobe &l, int flags) { return (l.type & flags) == l.type; }  // BxDF::MatchesFlags
+
+PG_HD Spec microReflF(const Lobe &l, V3 wo, V3 wi) {  // MicrofacetReflection::f
+    float cosThetaO = absCosTheta(wo), cosThetaI = absCosTheta(wi);
+    V3 wh = wi + wo;
+    if (cosThetaI == 0 || cosThetaO == 0) return spec(0.f);
+    if (wh.x == 0 && wh.y == 0 && wh.z == 0) return spec(0.f);
+    wh = normalize(wh);
+    float F = frDielectric(dot(wi, faceforward(wh, v3(0, 0, 1))), l.etaA, l.etaB);
+    return l.R * trD(l.a, l.b, wh) * trG(l.a, l.b, wo, wi) * F / (4 * cosThetaI * cosThetaO);
+}
+
+PG_HD Spec microTransF(const Lobe &l, V3 wo, V3 wi) {  // MicrofacetTransmission::f, TransportMode::Radiance
+    if (sameHemisphere(wo, wi)) return spec(0.f);
+    float cosThetaO = cosTheta(wo), cosThetaI = cosTheta(wi);
+    if (cosThetaI == 0 || cosThetaO == 0) return spec(0.f);
+    float eta = cosTheta(wo) > 0 ? (l.etaB / l.etaA) : (l.etaA / l.etaB);
+    V3 wh = normalize(wo + wi * eta);
+    if (wh.z < 0) wh = -wh;
+    if (dot(wo, wh) * dot(wi, wh) > 0) return spec(0.f);
+    float F = frDielectric(dot(wo, wh), l.etaA, l.etaB);
+    float sqrtDenom = dot(wo, wh) + eta * dot(wi, wh);
+    float factor = 1 / eta;
+    return (spec(1.f) - spec(F)) * l.R *
+           fabsf(trD(l.a, l.b, wh) * trG(l.a, l.b, wo, wi) * eta * eta * absDot(wi, wh) * absDot(wo, wh) * factor * factor /
+                 (cosThetaI * cosThetaO * sqrtDenom * sqrtDenom));
+}
+
+PG_HD float microTransPdf(const Lobe &l, V3 wo, V3 wi) {
+    if (sameHemisphere(wo, wi)) return 0;
+    float eta = cosTheta(wo) > 0 ? (l.etaB / l.etaA) : (l.etaA / l.etaB);
+    V3 wh = normalize(wo + wi * eta);
+    if (dot(wo, wh) * dot(wi, wh) > 0) return 0;
+    float sqrtDenom = dot(wo, wh) + eta * dot(wi, wh);
+    float dwh_dwi = fabsf((eta * eta * dot(wi, wh)) / (sqrtDenom * sqrtDenom));
+    return trPdf(l.a, l.b, wo, wh) * dwh_dwi;
+}
+
+PG_HD Spec orenNayarF(const Lobe &l, V3 wo, V3 wi) {
+    float sinThetaI = sinTheta(wi), sinThetaO = sinTheta(wo);
+    float maxCos = 0;
+    if (sinThetaI > 1e-4 && sinThetaO > 1e-4) {
+        float sinPhiI = sinPhi(wi), cosPhiI = cosPhi(wi);
+        float sinPhiO = sinPhi(wo), cosPhiO = cosPhi(wo);
+        float dCos = cosPhiI * cosPhiO + sinPhiI * sinPhiO;
+        maxCos = maxf(0.f, dCos);
+    }
+    float sinAlpha, tanBeta;
+    if (absCosTheta(wi) > absCosTheta(wo)) {
+        sinAlpha = sinThetaO;
+        tanBeta = sinThetaI / absCosTheta(wi);
+    } else {
+        sinAlpha = sinThetaI;
+        tanBeta = sinThetaO / absCosTheta(wo);
+    }
+    return l.R * kInvPi * (l.a + l.b * maxCos * sinAlpha * tanBeta);
+}
+
+PG_HD Spec lobeF(const Lobe &l, V3 wo, V3 wi) {
+    switch (l.kind) {
+    case LOBE_LAMBERT: return l.R * kInvPi;
+    case LOBE_OREN_NAYAR: return orenNayarF(l, wo, wi);
+    case LOBE_MICRO_REFL: return microReflF(l, wo, wi);
+    case LOBE_MICRO_TRANS: return microTransF(l, wo, wi);
+    default: return spec(0.f);  // specular lobes
+    }
+}
+
+PG_HD float lobePdf(const Lobe &l, V3 wo, V3 wi) {
+    switch (l.kind) {
+    case LOBE_LAMBERT:
+    case LOBE_OREN_NAYAR: return sameHemisphere(wo, wi) ? absCosTheta(wi) * kInvPi : 0;
+    case LOBE_MICRO_REFL: {
+        if (!sameHemisphere(wo, wi)) return 0;
+        V3 wh = normalize(wo + wi);
+        return trPdf(l.a, l.b, wo, wh) / (4 * dot(wo, wh));
+    }
+    case LOBE_MICRO_TRANS: return microTransPdf(l, wo, wi);
+    default: return 0;
+    }
+}
+
+// BxDF::Sample_f of each lobe; *pdf must be 0 on entry (BSDF::Sample_f sets it).
+PG_HD Spec lobeSample(const Lobe &l, V3 wo, float u0, float u1, V3 *wi, float *pdf, int *sampledType) {
+    switch (l.kind) {
+    case LOBE_LAMBERT:
+    case LOBE_OREN_NAYAR:
+        *wi = cosineSampleHemisphere(u0, u1);
+        if (wo.z < 0) wi->z *= -1;
+        *pdf = lobePdf(l, wo, *wi);
+        return lobeF(l, wo, *wi);
+    case LOBE_MICRO_REFL: {
+        if (wo.z == 0) return spec(0.f);
+        V3 wh = trSampleWh(l.a, l.b, wo, u0, u1);
+        if (dot(wo, wh) < 0) return spec(0.f);
+        *wi = reflectAbout(wo, wh);
+        if (!sameHemisphere(wo, *wi)) return spec(0.f);
+        *pdf = trPdf(l.a, l.b, wo, wh) / (4 * dot(wo, wh));
+        return microReflF(l, wo, *wi);
+    }
+    case LOBE_MICRO_TRANS: {
+        if (wo.z == 0) return spec(0.f);
+        V3 wh = trSampleWh(l.a, l.b, wo, u0, u1);
+        if (dot(wo, wh) < 0) return spec(0.f);
+        float eta = cosTheta(wo) > 0 ? (l.etaA / l.etaB) : (l.etaB / l.etaA);
+        if (!refract(wo, wh, eta, wi)) return spec(0.f);
+        *pdf = microTransPdf(l, wo, *wi);
+        return microTransF(l, wo, *wi);
+    }
+    case LOBE_FRESNEL_SPECULAR: {
+        float F = frDielectric(cosTheta(wo), l.etaA, l.etaB);
+        if (u0 < F) {
+            *wi = v3(-wo.x, -wo.y, wo.z);
+            *sampledType = BSDF_SPECULAR | BSDF_REFLECTION;
+            *pdf = F;
+            return F * l.R / absCosTheta(*wi);
+        }
+        bool entering = cosTheta(wo) > 0;
+        float etaI = entering ? l.etaA : l.etaB;
+        float etaT = entering ? l.etaB : l.etaA;
+        if (!refract(wo, faceforward(v3(0, 0, 1), wo), etaI / etaT, wi)) return spec(0.f);
+        Spec ft = l.T * (1 - F);
+        ft *= (etaI * etaI) / (etaT * etaT);
+        *sampledType = BSDF_SPECULAR | BSDF_TRANSMISSION;
+        *pdf = 1 - F;
+        return ft / absCosTheta(*wi);
+    }
+    default: {  // LOBE_SPEC_REFL_NOOP: SpecularReflection with FresnelNoOp
+        *wi = v3(-wo.x, -wo.y, wo.z);
+        *pdf = 1;
+        return spec(1.f) * l.R / absCosTheta(*wi);
+    }
+    }
+}
+
+PG_HD V3 bsdfWorldToLocal(const BSDF &b, V3 v) { return v3(dot(v, b.ss), dot(v, b.ts), dot(v, b.ns)); }
+PG_HD V3 bsdfLocalToWorld(const BSDF &b, V3 v) {
+    return v3(b.ss.x * v.x + b.ts.x * v.y + b.ns.x * v.z, b.ss.y * v.x + b.ts.y * v.y + b.ns.y * v.z,
+              b.ss.z * v.x + b.ts.z * v.y + b.ns.z * v.z);
+}
+PG_HD int bsdfNumComponents(const BSDF &b, int flags) {
+    int n = 0;
+    for (int i = 0; i < b.nLobes; ++i)
+        if (lobeMatches(b.lobes[i], flags)) ++n;
+    return n;
+}
+
+PG_HD Spec bsdfF(const BSDF &b, V3 woW, V3 wiW, int flags) {
+    V3 wi = bsdfWorldToLocal(b, wiW), wo = bsdfWorldToLocal(b, woW);
+    if (wo.z == 0) return spec(0.f);
+    bool reflect = dot(wiW, b.ng) * dot(woW, b.ng) > 0;
+    Spec f = spec(0.f);
+    for (int i = 0; i < b.nLobes; ++i)
+        if (lobeMatches(b.lobes[i], flags) && ((reflect && (b.lobes[i].type & BSDF_REFLECTION)) ||
+                                               (!reflect && (b.lobes[i].type & BSDF_TRANSMISSION))))
+            f += lobeF(b.lobes[i], wo, wi);
+    return f;
+}
+
+PG_HD float bsdfPdf(const BSDF &b, V3 woW, V3 wiW, int flags) {
+    if (b.nLobes == 0) return 0.f;
+    V3 wo = bsdfWorldToLocal(b, woW), wi = bsdfWorldToLocal(b, wiW);
+    if (wo.z == 0) return 0.f;
+    float pdf = 0.f;
+    int matchingComps = 0;
+    for (int i = 0; i < b.nLobes; ++i)
+        if (lobeMatches(b.lobes[i], flags)) {
+            ++matchingComps;
+            pdf += lobePdf(b.lobes[i], wo, wi);
+        }
+    return matchingComps > 0 ? pdf / matchingComps : 0.f;
+}
+
+PG_HD Spec bsdfSampleF(const BSDF &b, V3 woW, V3 *wiW, float u0, float u1, float *pdf, int type, int *sampledType) {
+    int matchingComps = bsdfNumComponents(b, type);
+    if (matchingComps == 0) {
+        *pdf = 0;
+        *sampledType = 0;
+        return spec(0.f);
+    }
+    int comp = (int)floorf(u0 * matchingComps);
+    if (comp > matchingComps - 1) comp = matchingComps - 1;
+    int which = -1, count = comp;
+    for (int i = 0; i < b.nLobes; ++i)
+        if (lobeMatches(b.lobes[i], type) && count-- == 0) {
+            which = i;
+            break;
+        }
+    const Lobe &bx = b.lobes[which];
+    float uR = minf(u0 * matchingComps - comp, kOneMinusEpsilon);
+    V3 wi, wo = bsdfWorldToLocal(b, woW);
+    // the reference returns here without touching *pdf / *sampledType (reflection.cpp:779);
+    // the caller's values are then whatever they held -- zero both so the path ends the same way
+    if (wo.z == 0) {
+        *pdf = 0;
+        *sampledType = 0;
+        return spec(0.f);
+    }
+    *pdf = 0;
+    *sampledType = bx.type;
+    Spec f = lobeSample(bx, wo, uR, u1, &wi, pdf, sampledType);
+    if (*pdf == 0) {
+        *sampledType = 0;
+        return spec(0.f);
+    }
+    *wiW = bsdfLocalToWorld(b, wi);
+    if (!(bx.type & BSDF_SPECULAR) && matchingComps > 1)
+        for (int i = 0; i < b.nLobes; ++i)
+            if (i != which && lobeMatches(b.lobes[i], type)) *pdf += lobePdf(b.lobes[i], wo, wi);
+    if (matchingComps > 1) *pdf /= matchingComps;
+    if (!(bx.type & BSDF_SPECULAR)) {
+        bool reflect = dot(*wiW, b.ng) * dot(woW, b.ng) > 0;
+        f = spec(0.f);
+        for (int i = 0; i < b.nLobes; ++i)
+            if (lobeMatches(b.lobes[i], type) && ((reflect && (b.lobes[i].type & BSDF_REFLECTION)) ||
+                                                  (!reflect && (b.lobes[i].type & BSDF_TRANSMISSION))))
+                f += lobeF(b.lobes[i], wo, wi);
+    }
+    return f;
+}
+
+// Material::ComputeScatteringFunctions for the material table of pbrtgpu.h
+// (allowMultipleLobes = true, TransportMode::Radiance, as path.cpp:107 calls it).
+// wvl0 = hero wavelength in nm, used by dispersive_glass only.
+PG_HD void makeBSDF(const SurfInt &it, int tag, const float *mp, float wvl0, BSDF *b) {
+    b->ns = it.ns;
+    b->ng = it.n;
+    b->ss = normalize(it.dpdus);
+    b->ts = cross(b->ns, b->ss);
+    b->eta = 1;
+    b->nLobes = 0;
+    if (tag == PBRTGPU_MAT_MATTE) {
+        Spec r = loadSpec(mp);
+        float sig = PG_LD(mp + 3);
+        if (!isBlack(r)) {
+            Lobe &l = b->lobes[b->nLobes++];
+            l.type = BSDF_REFLECTION | BSDF_DIFFUSE;
+            l.R = r;
+            if (sig == 0) l.kind = LOBE_LAMBERT;
+            else {
+                l.kind = LOBE_OREN_NAYAR;
+                float sigma = radians(sig);
+                float sigma2 = sigma * sigma;
+                l.a = 1.f - (sigma2 / (2.f * (sigma2 + 0.33f)));
+                l.b = 0.45f * sigma2 / (sigma2 + 0.09f);
+            }
+        }
+    } else if (tag == PBRTGPU_MAT_PLASTIC) {
+        Spec kd = loadSpec(mp), ks = loadSpec(mp + 3);
+        if (!isBlack(kd)) {
+            Lobe &l = b->lobes[b->nLobes++];
+            l.kind = LOBE_LAMBERT;
+            l.type = BSDF_REFLECTION | BSDF_DIFFUSE;
+            l.R = kd;
+        }
+        if (!isBlack(ks)) {
+            Lobe &l = b->lobes[b->nLobes++];
+            l.kind = LOBE_MICRO_REFL;
+            l.type = BSDF_REFLECTION | BSDF_GLOSSY;
+            l.R = ks;
+            l.a = l.b = PG_LD(mp + 6);
+            l.etaA = 1.5f, l.etaB = 1.f;
+        }
+    } else if (tag == PBRTGPU_MAT_GLASS || tag == PBRTGPU_MAT_DISPERSIVE_GLASS) {
+        Spec R = loadSpec(mp), T = loadSpec(mp + 3);
+        float eta;
+        if (tag == PBRTGPU_MAT_GLASS) eta = PG_LD(mp + 8);
+        else eta = PG_LD(mp + 8) + PG_LD(mp + 10) / (wvl0 * wvl0);  // cauchyB + cauchyC / lambda^2
+        b->eta = eta;
+        if (isBlack(R) && isBlack(T)) return;
+        bool isSpecular = PG_LD(mp + 9) != 0.f;
+        if (isSpecular) {
+            Lobe &l = b->lobes[b->nLobes++];
+            l.kind = LOBE_FRESNEL_SPECULAR;
+            l.type = BSDF_REFLECTION | BSDF_TRANSMISSION | BSDF_SPECULAR;
+            l.R = R, l.T = T;
+            l.etaA = 1.f, l.etaB = eta;
+        } else {
+            float ax = PG_LD(mp + 6), ay = PG_LD(mp + 7);
+            if (!isBlack(R)) {
+                Lobe &l = b->lobes[b->nLobes++];
+                l.kind = LOBE_MICRO_REFL;
+                l.type = BSDF_REFLECTION | BSDF_GLOSSY;
+                l.R = R;
+                l.a = ax, l.b = ay;
+                l.etaA = 1.f, l.etaB = eta;
+            }
+            if (!isBlack(T)) {
+                Lobe &l = b->lobes[b->nLobes++];
+                l.kind = LOBE_MICRO_TRANS;
+                l.type = BSDF_TRANSMISSION | BSDF_GLOSSY;
+                l.R = T;
+                l.a = ax, l.b = ay;
+                l.etaA = 1.f, l.etaB = eta;
+            }
+        }
+    } else if (tag == PBRTGPU_MAT_MIRROR) {
+        Spec R = loadSpec(mp);
+        if (!isBlack(R)) {
+            Lobe &l = b->lobes[b->nLobes++];
+            l.kind = LOBE_SPEC_REFL_NOOP;
+            l.type = BSDF_REFLECTION | BSDF_SPECULAR;
+            l.R = R;
+        }
+    }
+}
+
+}  // namespace pg
+#endif

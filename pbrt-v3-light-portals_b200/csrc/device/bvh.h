@@ -58,7 +58,7 @@ struct DevBVH {
 
 struct Hit {
     int prim;  // BVH-order slot, -1 = miss
-    float t, b0, b1;
+    float t, b0, b1, b2;
 };
 
 struct TraverseCounters {  // filled only by the instrumented oracle build
@@ -132,11 +132,11 @@ PG_HD bool traverse(const DevBVH &bvh, Ray &ray, Hit *hit, TraverseCounters *cnt
                 int tag = f2i(a.w);
                 int type = tag & kTagTypeMask;
                 if (COUNT) cnt->prims += 1;
-                float t, b0 = 0, b1 = 0;
+                float t, b0 = 0, b1 = 0, b2 = 0;
                 bool h;
                 if (type == 0) {
                     F4 b = PG_LDG(tp + 1), c = PG_LDG(tp + 2);
-                    h = triangleTest(ray, v3(a.x, a.y, a.z), v3(b.x, b.y, b.z), v3(c.x, c.y, c.z), &t, &b0, &b1);
+                    h = triangleTest(ray, v3(a.x, a.y, a.z), v3(b.x, b.y, b.z), v3(c.x, c.y, c.z), &t, &b0, &b1, &b2);
                     if (!ANY && (tag & kTagDegenerate)) h = false;
                 } else if (type == 1) {
                     h = aaplaneTest(ray, bvh.planeParams + 48 * (size_t)(tag >> kTagShapeShift), &t, nullptr);
@@ -151,6 +151,7 @@ PG_HD bool traverse(const DevBVH &bvh, Ray &ray, Hit *hit, TraverseCounters *cnt
                     hit->t = t;
                     hit->b0 = b0;
                     hit->b1 = b1;
+                    hit->b2 = b2;
                 }
                 if (tag & kTagLast) break;
             }

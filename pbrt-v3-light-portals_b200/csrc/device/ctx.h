@@ -10,34 +10,9 @@
 #include <vector>
 
 #include "../../../include/pbrtgpu.h"
-#include "bvh.h"
+#include "ctx_scene.h"
 
 namespace pg {
-
-// Everything a kernel needs to know about the scene; passed by value.
-struct DevScene {
-    DevBVH bvh;
-    int nPrims, nLights, nMaterials;
-    const int *primOrigId;
-    const int *primMaterial;
-    const int *primLight;
-    const unsigned char *primFlags;
-    const float *triN;   // 9 per slot or null
-    const float *triUV;  // 6 per slot or null
-    const float *triS;   // 9 per slot or null
-    const int *matTag;
-    const float *matParams;
-    const int *lightTag;
-    const int *lightPrim;
-    const int *lightStrategy;
-    const int *lightPortalBegin;
-    const float *lightParams;
-    const float *portalParams;
-    const float *lightCdf;  // nLights+1 (power strategy) or null
-    float lightFuncInt;
-    const float *lightFunc;
-    float worldCenter[3], worldRadius;
-};
 
 struct DeviceBuffer {
     void *p = nullptr;
@@ -56,6 +31,14 @@ struct pbrtgpu_ctx {
     std::vector<void *> sceneAllocs;  // freed on re-upload / destroy
     // Halton tables (uploaded at create)
     unsigned short *dPerms = nullptr;
+    int *dPrimes = nullptr, *dPrimeSums = nullptr;  // first 1000 primes and their running sums
+    // wavefront state of the path integrator (render.cu), grown on demand
+    pg::DeviceBuffer wave[24];
+    pg::DeviceBuffer lightDist;                     // {func[n], cdf[n+1]} x {uniform, power}: the light-pick distributions
+    float lightFuncInt[2] = {0, 0};
+    pg::DeviceBuffer filterTable;
+    unsigned long long *dTotals = nullptr;          // cameraRays, closestRays, shadowRays, scrubbed
+    bool hasNullMaterial = false;                   // some primitive has no material (path.cpp:108-113)
     // render scratch, grown on demand
     pg::DeviceBuffer scratch[16];
     pg::DeviceBuffer film;

@@ -1,0 +1,214 @@
+// Direct lighting at a path vertex, split in two: this file GENERATES the
+// next-event rays (what the reference does before it calls Scene::Intersect /
+// IntersectP) and states how each is RESOLVED once traced.
+//   UniformSampleOneLight                    core/integrator.cpp:100-122
+//   EstimateDirect (stock MIS)               core/integrator.cpp:124-258
+//   PortalArealight::EstimateDirect{,Light,Portal,Proj}   lights/portal_arealight.cpp:29-239
+//   Distribution1D::SampleDiscrete, FindInterval          core/sampling.h:90-101, core/pbrt.h:408-420
+#ifndef PG_DEVICE_DIRECT_H
+#define PG_DEVICE_DIRECT_H
+
+#include "ctx_scene.h"
+#include "portal.h"
+
+namespace pg {
+
+// How a traced next-event ray turns into radiance.
+enum NeeMode {
+    NEE_MIS_LIGHT = 0,     // closest hit; counts only if the hit primitive carries `light`; a miss counts light->Le(ray) (infinite lights)
+    NEE_ANY_EMITTER = 1,   // closest hit; whatever emitter is hit counts (portal estimators, Q6); a miss counts nothing
+    NEE_ANY_OR_LIGHT = 2   // as 1, but a miss keeps the sampled light's own L (EstimateDirectLight, portal_arealight.cpp:139-145)
+};
+
+struct NeeRequest {
+    bool hasShadow;  // any-hit ray: add shadowContrib if unoccluded
+    Ray shadowRay;
+    Spec shadowContrib;
+    bool hasClosest;  // closest-hit ray: add closestContrib * Li(resolved by mode)
+    Ray closestRay;
+    Spec closestContrib;
+    int light, mode;
+};
+
+PG_HD int findIntervalCdf(const float *cdf, int size, float u) {  // FindInterval(size, cdf[i] <= u)
+    int first = 0, len = size;
+    while (len > 0) {
+        int half = len >> 1, middle = first + half;
+        if (PG_LD(cdf + middle) <= u) {
+            first = middle + 1;
+            len -= half + 1;
+        } else
+            len = half;
+    }
+    int r = first - 1;
+    return r < 0 ? 0 : (r > size - 2 ? size - 2 : r);
+}
+
+// DiffuseAreaLight::L for light `li` seen from direction w at a point with normal n
+PG_HD Spec areaLightL(const DevScene &sc, int li, V3 n, V3 w) {
+    const float *lp = sc.lightParams + PBRTGPU_LIGHT_STRIDE * (size_t)li;
+    bool twoSided = PG_LD(lp + 3) != 0.f;
+    return (twoSided || dot(n, w) > 0) ? loadSpec(lp) : spec(0.f);
+}
+
+// Light::Sample_Li.  Returns Li; fills wi, pdf and the point the visibility ray aims at.
+PG_HD Spec lightSampleLi(const DevScene &sc, int li, const SurfInt &it, float u0, float u1, V3 *wi, float *pdf, ShapeSample *pL) {
+    int tag = PG_LD(sc.lightTag + li);
+    const float *lp = sc.lightParams + PBRTGPU_LIGHT_STRIDE * (size_t)li;
+    pL->pError = v3(0, 0, 0);
+    pL->n = v3(0, 0, 0);
+    if (tag == PBRTGPU_LIGHT_DIFFUSE_AREA || tag == PBRTGPU_LIGHT_PORTAL_AREA) {
+        int slot = PG_LD(sc.lightPrim + li);
+        int flags = sc.primFlags ? PG_LD(sc.primFlags + slot) : 0;
+        *pL = shapeSampleRef(sc.bvh, slot, flags, sc.triN, it.p, it.pError, it.n, u0, u1, pdf);
+        if (*pdf == 0 || lengthSquared(pL->p - it.p) == 0) {
+            *pdf = 0;
+            return spec(0.f);
+        }
+        *wi = normalize(pL->p - it.p);
+        return areaLightL(sc, li, pL->n, -*wi);
+    }
+    if (tag == PBRTGPU_LIGHT_INFINITE) {
+        float uv[2];
+        Spec L = infiniteSampleLi(lp, u0, u1, wi, pdf, uv);
+        pL->p = it.p + *wi * (2 * sc.worldRadius);
+        return L;
+    }
+    if (tag == PBRTGPU_LIGHT_POINT) {
+        V3 pLight = loadV3(lp + 3);
+        *wi = normalize(pLight - it.p);
+        *pdf = 1.f;
+        pL->p = pLight;
+        return loadSpec(lp) / distanceSquared(pLight, it.p);
+    }
+    // PBRTGPU_LIGHT_DISTANT
+    V3 wLight = loadV3(lp + 3);
+    *wi = wLight;
+    *pdf = 1;
+    pL->p = it.p + wLight * (2 * sc.worldRadius);
+    return loadSpec(lp);
+}
+
+PG_HD float lightPdfLi(const DevScene &sc, int li, const SurfInt &it, V3 wi) {
+    int tag = PG_LD(sc.lightTag + li);
+    if (tag == PBRTGPU_LIGHT_DIFFUSE_AREA || tag == PBRTGPU_LIGHT_PORTAL_AREA)
+        return shapePdfRef(sc.bvh, PG_LD(sc.lightPrim + li), it.p, it.pError, it.n, wi);
+    if (tag == PBRTGPU_LIGHT_INFINITE) return infinitePdfLi(sc.lightParams + PBRTGPU_LIGHT_STRIDE * (size_t)li, wi);
+    return 0;
+}
+
+PG_HD float powerHeuristic(float fPdf, float gPdf) {  // PowerHeuristic(1, f, 1, g)
+    float f = 1 * fPdf, g = 1 * gPdf;
+    return (f * f) / (f * f + g * g);
+}
+
+// The portal branch of EstimateDirect.  u1 is what the reference passes as u1:
+// the SCATTERING sample (Q5); u2 is unused there as well.
+PG_HD void estimateDirectPortal(const DevScene &sc, int li, const SurfInt &it, const BSDF &bsdf, float u1x, float u1y,
+                                Spec scale, NeeRequest *out) {
+    const int flagsNS = BSDF_ALL & ~BSDF_SPECULAR;
+    int strat = PG_LD(sc.lightStrategy + li);
+    int slot = PG_LD(sc.lightPrim + li);
+    int tag = f2i(PG_LDG(sc.bvh.tris + 3 * (size_t)slot).w);
+    const float *lightRec = sc.bvh.planeParams + 48 * (size_t)(tag >> kTagShapeShift);
+    int sel = -2;
+    float portalPdf = 1;
+    int pBegin = PG_LD(sc.lightPortalBegin + li), nPortals = PG_LD(sc.lightPortalBegin + li + 1) - pBegin;
+    const float *portals = sc.portalParams + PBRTGPU_PORTAL_STRIDE * (size_t)pBegin;
+    M44 w2o = loadM44(lightRec + 32);
+    if (strat != PBRTGPU_PORTAL_UNIFORM_LIGHT) {
+        // with no portal at all the loop leaves behindAll = true -> light sampling
+        sel = nPortals > 0 ? portalSelect(portals, nPortals, w2o, it.p, u1x, &portalPdf) : -2;
+        if (sel == -1) return;
+        if (sel >= 0 && !portalInFront(loadPortal(portals + PBRTGPU_PORTAL_STRIDE * sel), w2o, it.p)) sel = -2;
+    }
+    V3 wi = v3(0, 0, 0);
+    float pdf = 0;
+    if (sel == -2) {  // EstimateDirectLight
+        ShapeSample pL;
+        Spec Li = lightSampleLi(sc, li, it, u1x, u1y, &wi, &pdf, &pL);
+        if (isBlack(Li) || !(pdf > 0)) return;
+        out->mode = NEE_ANY_OR_LIGHT;
+    } else if (strat == PBRTGPU_PORTAL_UNIFORM_PORTAL) {
+        portalSampleUniform(loadPortal(portals + PBRTGPU_PORTAL_STRIDE * sel), loadM44(lightRec + 16), it.p, u1x, u1y, &wi, &pdf);
+        if (!(pdf > 0)) return;
+        out->mode = NEE_ANY_EMITTER;
+    } else {  // projection
+        portalSampleProj(loadPortal(portals + PBRTGPU_PORTAL_STRIDE * sel), loadPlane(lightRec), w2o, it.p, u1x, &wi, &pdf);
+        if (!(pdf > 0)) return;
+        out->mode = NEE_ANY_EMITTER;
+    }
+    Spec f = bsdfF(bsdf, it.wo, wi, flagsNS) * absDot(wi, it.ns);
+    if (isBlack(f)) return;
+    Spec Ld = f / pdf;  // times Li when the ray comes back
+    if (sel >= 0 && strat == PBRTGPU_PORTAL_PROJECTION) Ld = Ld / portalPdf;  // only this strategy divides (Q8)
+    out->hasClosest = true;
+    out->closestRay = spawnRay(it.p, it.pError, it.n, wi);
+    out->closestContrib = scale * Ld;
+    out->light = li;
+}
+
+// UniformSampleOneLight + EstimateDirect, up to the rays.  `scale` = beta;
+// the pick probability is folded in here.
+PG_HD void sampleOneLight(const DevScene &sc, const HaltonParams &hal, PathSampler &smp, const SurfInt &it, const BSDF &bsdf,
+                          Spec beta, NeeRequest *out) {
+    out->hasShadow = out->hasClosest = false;
+    out->light = -1;
+    out->mode = NEE_MIS_LIGHT;
+    if (sc.nLights == 0) return;
+    float uPick = get1D(hal, smp);
+    int li = findIntervalCdf(sc.lightCdf, sc.nLights + 1, uPick);
+    float pickPdf = (sc.lightFuncInt > 0) ? PG_LD(sc.lightFunc + li) / (sc.lightFuncInt * sc.nLights) : 0;
+    if (pickPdf == 0) return;
+    float uL0, uL1, uS0, uS1;
+    get2D(hal, smp, &uL0, &uL1);
+    get2D(hal, smp, &uS0, &uS1);
+    int tag = PG_LD(sc.lightTag + li);
+    if (tag == PBRTGPU_LIGHT_PORTAL_AREA) {
+        NeeRequest r = *out;
+        estimateDirectPortal(sc, li, it, bsdf, uS0, uS1, spec(1.f), &r);
+        if (r.hasClosest) r.closestContrib = beta * (r.closestContrib / pickPdf);
+        *out = r;
+        return;
+    }
+    const int flagsNS = BSDF_ALL & ~BSDF_SPECULAR;
+    bool isDelta = tag == PBRTGPU_LIGHT_POINT || tag == PBRTGPU_LIGHT_DISTANT;
+    V3 wi = v3(0, 0, 0);  // Vector3f() is zero-initialised
+    float lightPdf = 0, scatteringPdf = 0;
+    ShapeSample pL;
+    Spec Li = lightSampleLi(sc, li, it, uL0, uL1, &wi, &lightPdf, &pL);
+    if (lightPdf > 0 && !isBlack(Li)) {
+        Spec f = bsdfF(bsdf, it.wo, wi, flagsNS) * absDot(wi, it.ns);
+        scatteringPdf = bsdfPdf(bsdf, it.wo, wi, flagsNS);
+        if (!isBlack(f)) {
+            Spec Ld;
+            if (isDelta) Ld = f * Li / lightPdf;
+            else Ld = f * Li * powerHeuristic(lightPdf, scatteringPdf) / lightPdf;
+            out->hasShadow = true;
+            out->shadowRay = spawnRayTo(it.p, it.pError, it.n, pL.p, pL.pError, pL.n);
+            out->shadowContrib = beta * (Ld / pickPdf);
+        }
+    }
+    if (!isDelta) {
+        int sampledType;
+        Spec f = bsdfSampleF(bsdf, it.wo, &wi, uS0, uS1, &scatteringPdf, flagsNS, &sampledType);
+        f *= absDot(wi, it.ns);
+        bool sampledSpecular = (sampledType & BSDF_SPECULAR) != 0;
+        if (!isBlack(f) && scatteringPdf > 0) {
+            float weight = 1;
+            if (!sampledSpecular) {
+                lightPdf = lightPdfLi(sc, li, it, wi);
+                if (lightPdf == 0) return;
+                weight = powerHeuristic(scatteringPdf, lightPdf);
+            }
+            out->hasClosest = true;
+            out->closestRay = spawnRay(it.p, it.pError, it.n, wi);
+            out->closestContrib = beta * ((f * weight / scatteringPdf) / pickPdf);
+            out->light = li;
+            out->mode = NEE_MIS_LIGHT;
+        }
+    }
+}
+
+}  // namespace pg
+#endif

@@ -1,0 +1,179 @@
+// Second half of integrator.h: shade, next-event resolve, film.
+#ifndef PG_DEVICE_INTEGRATOR_STAGES_H
+#define PG_DEVICE_INTEGRATOR_STAGES_H
+
+namespace pg {
+
+// ---- stage 3: one path vertex (the body of path.cpp:81-187 after scene.Intersect).
+// pos = position in the depth-d closest-hit queue; cur = which of the two
+// ping-pong queues holds depth d.
+PG_HD void stageShade(const WaveParams &w, int depth, int cur, int pos) {
+    int slot = w.qSlot[cur][pos];
+    Ray ray = loadRay(w.rays[cur], pos);
+    F4 hit = w.hits[pos];
+    int prim = f2i(hit.x);
+    F4 Lq = w.L[slot], bq = w.beta[slot];
+    Spec L = spec(Lq.x, Lq.y, Lq.z), beta = spec(bq.x, bq.y, bq.z);
+    float wvl0 = Lq.w, etaScale = bq.w;
+    int flags = w.flags[slot];
+    int bounces = flags & 255;
+    bool specularBounce = (flags >> 8) & 1;
+    bool found = prim >= 0;
+    SurfInt it;
+    if (found) it = hitInteraction(w.sc, prim, hit.y, hit.z, hit.w, ray);
+
+    // emitted light at the vertex or from the environment (path.cpp:91-101)
+    if (bounces == 0 || specularBounce) {
+        if (found) L += beta * hitLe(w.sc, prim, it.n, -ray.d);
+        else
+            for (int i = 0; i < w.sc.nLights; ++i)
+                if (PG_LD(w.sc.lightTag + i) == PBRTGPU_LIGHT_INFINITE)
+                    L += beta * infiniteLe(w.sc.lightParams + PBRTGPU_LIGHT_STRIDE * (size_t)i, ray.d);
+    }
+    bool alive = found && bounces < w.maxDepth;
+    Ray next;
+    if (alive) {
+        if (it.wvlsLost) wvl0 = 0.f;  // Transform::operator()(SurfaceInteraction) leaves wvls default-constructed
+        int mat = w.sc.primMaterial ? PG_LD(w.sc.primMaterial + prim) : -1;
+        if (mat < 0) {
+            // no material: skip the boundary, same bounce count (path.cpp:108-113)
+            next = spawnRay(it.p, it.pError, it.n, ray.d);
+        } else {
+            PathSampler smp;
+            smp.index = w.hIndex[slot];
+            smp.dim = w.dim[slot];
+            BSDF bsdf;
+            makeBSDF(it, PG_LD(w.sc.matTag + mat), w.sc.matParams + PBRTGPU_MAT_STRIDE * (size_t)mat, wvl0, &bsdf);
+            if (bsdfNumComponents(bsdf, BSDF_ALL & ~BSDF_SPECULAR) > 0) {
+                NeeRequest nee;
+                sampleOneLight(w.sc, w.hal, smp, it, bsdf, beta, &nee);
+                if (nee.hasShadow) {
+                    int sp = atomicIncInt(&w.cnt->nShadow[depth]);
+                    storeRay(w.shadowRays, sp, nee.shadowRay);
+                    w.shadowContrib[sp] = f4(nee.shadowContrib.r, nee.shadowContrib.g, nee.shadowContrib.b, bitsToFloat((unsigned)slot));
+                }
+                if (nee.hasClosest) {
+                    int np = atomicIncInt(&w.cnt->nNee[depth]);
+                    storeRay(w.neeRays, np, nee.closestRay);
+                    w.neeContrib[np] = f4(nee.closestContrib.r, nee.closestContrib.g, nee.closestContrib.b, bitsToFloat((unsigned)slot));
+                    w.neeInfo[2 * (size_t)np] = nee.light;
+                    w.neeInfo[2 * (size_t)np + 1] = nee.mode;
+                }
+            }
+            // sample the BSDF for the next direction (path.cpp:131-151)
+            V3 wo = -ray.d, wi = v3(0, 0, 0);
+            float pdf, u0, u1;
+            int sampled;
+            get2D(w.hal, smp, &u0, &u1);
+            Spec f = bsdfSampleF(bsdf, wo, &wi, u0, u1, &pdf, BSDF_ALL, &sampled);
+            if (isBlack(f) || pdf == 0.f) alive = false;
+            else {
+                beta *= f * absDot(wi, it.ns) / pdf;
+                specularBounce = (sampled & BSDF_SPECULAR) != 0;
+                if ((sampled & BSDF_SPECULAR) && (sampled & BSDF_TRANSMISSION)) {
+                    float eta = bsdf.eta;
+                    etaScale *= (dot(wo, it.n) > 0) ? (eta * eta) : 1 / (eta * eta);
+                }
+                next = spawnRay(it.p, it.pError, it.n, wi);
+                // Russian roulette (path.cpp:177-184)
+                Spec rrBeta = beta * etaScale;
+                if (maxComponentValue(rrBeta) < w.rrThreshold && bounces > 3) {
+                    float q = maxf(.05f, 1 - maxComponentValue(rrBeta));
+                    if (get1D(w.hal, smp) < q) alive = false;
+                    else beta /= 1 - q;
+                }
+                ++bounces;
+            }
+            w.dim[slot] = smp.dim;
+        }
+    }
+    w.L[slot] = f4(L.r, L.g, L.b, wvl0);
+    if (alive) {
+        w.beta[slot] = f4(beta.r, beta.g, beta.b, etaScale);
+        w.flags[slot] = (flags & ~0x1ff) | bounces | (specularBounce ? 256 : 0);
+        int np = atomicIncInt(&w.cnt->nActive[depth + 1]);
+        storeRay(w.rays[cur ^ 1], np, next);
+        w.qSlot[cur ^ 1][np] = slot;
+    }
+}
+
+// ---- stage 4a: shadow rays.  Unoccluded -> the light sample counts.
+PG_HD void stageShadowResolve(const WaveParams &w, int pos, bool occluded) {
+    if (occluded) return;
+    F4 c = w.shadowContrib[pos];
+    int slot = (int)floatToBits(c.w);
+    F4 Lq = w.L[slot];
+    Lq.x += c.x, Lq.y += c.y, Lq.z += c.z;
+    w.L[slot] = Lq;
+}
+
+// ---- stage 4b: closest-hit next-event rays (BSDF-sampled MIS ray, portal rays).
+PG_HD void stageNeeResolve(const WaveParams &w, int pos) {
+    F4 c = w.neeContrib[pos];
+    int slot = (int)floatToBits(c.w);
+    int light = w.neeInfo[2 * (size_t)pos], mode = w.neeInfo[2 * (size_t)pos + 1];
+    Ray ray = loadRay(w.neeRays, pos);
+    F4 hit = w.neeHits[pos];
+    int prim = f2i(hit.x);
+    Spec Li = spec(0.f);
+    if (prim >= 0) {
+        int hitLight = w.sc.primLight ? PG_LD(w.sc.primLight + prim) : -1;
+        if (hitLight >= 0 && (mode != NEE_MIS_LIGHT || hitLight == light)) {
+            SurfInt li = hitInteraction(w.sc, prim, hit.y, hit.z, hit.w, ray);
+            Li = areaLightL(w.sc, hitLight, li.n, -ray.d);
+        }
+    } else if (mode == NEE_MIS_LIGHT) {
+        if (PG_LD(w.sc.lightTag + light) == PBRTGPU_LIGHT_INFINITE)
+            Li = infiniteLe(w.sc.lightParams + PBRTGPU_LIGHT_STRIDE * (size_t)light, ray.d);
+    } else if (mode == NEE_ANY_OR_LIGHT)
+        Li = loadSpec(w.sc.lightParams + PBRTGPU_LIGHT_STRIDE * (size_t)light);
+    if (isBlack(Li)) return;
+    F4 Lq = w.L[slot];
+    Lq.x += c.x * Li.r, Lq.y += c.y * Li.g, Lq.z += c.z * Li.b;
+    w.L[slot] = Lq;
+}
+
+// ---- stage 5: scrub (integrator.cpp:592-613) + FilmTile::AddSample with atomics
+PG_HD void stageFilm(const WaveParams &w, int slot) {
+    if (!(w.flags[slot] & (1 << 9))) return;
+    F4 Lq = w.L[slot];
+    Spec L = spec(Lq.x, Lq.y, Lq.z);
+    bool bad = hasNaNs(L);
+    if (!bad && luminance(L) < -1e-5) bad = true;
+    if (!bad && isInfF(luminance(L))) bad = true;
+    if (bad) {
+        L = spec(0.f);
+        atomicAddU64(&w.cnt->scrubbed, 1ull);
+    }
+    const FilmParams &fp = w.film;
+    if (luminance(L) > fp.maxSampleLuminance) L *= fp.maxSampleLuminance / luminance(L);
+    float dx = w.pFilm[2 * (size_t)slot] - 0.5f, dy = w.pFilm[2 * (size_t)slot + 1] - 0.5f;
+    int p0x = (int)ceilf(dx - fp.radius[0]), p0y = (int)ceilf(dy - fp.radius[1]);
+    int p1x = (int)floorf(dx + fp.radius[0]) + 1, p1y = (int)floorf(dy + fp.radius[1]) + 1;
+    p0x = p0x > fp.cropped[0] ? p0x : fp.cropped[0];
+    p0y = p0y > fp.cropped[1] ? p0y : fp.cropped[1];
+    p1x = p1x < fp.cropped[2] ? p1x : fp.cropped[2];
+    p1y = p1y < fp.cropped[3] ? p1y : fp.cropped[3];
+    int width = fp.cropped[2] - fp.cropped[0];
+    for (int y = p0y; y < p1y; ++y) {
+        float fy = fabsf((y - dy) * fp.invRadius[1] * 16);
+        int iy = (int)floorf(fy);
+        iy = iy < 15 ? iy : 15;
+        for (int x = p0x; x < p1x; ++x) {
+            float fx = fabsf((x - dx) * fp.invRadius[0] * 16);
+            int ix = (int)floorf(fx);
+            ix = ix < 15 ? ix : 15;
+            float fw = PG_LD(fp.filterTable + iy * 16 + ix);
+            float *px = fp.rgbw + 4 * ((size_t)(y - fp.cropped[1]) * width + (x - fp.cropped[0]));
+            // pixel.contribSum += L * sampleWeight * filterWeight; sampleWeight (the camera ray weight) is 1
+            Spec c = L * 1.f * fw;
+            atomicAddFloat(px + 0, c.r);
+            atomicAddFloat(px + 1, c.g);
+            atomicAddFloat(px + 2, c.b);
+            atomicAddFloat(px + 3, fw);
+        }
+    }
+}
+
+}  // namespace pg
+#endif

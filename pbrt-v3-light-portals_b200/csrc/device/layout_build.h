@@ -11,6 +11,7 @@
 
 #include "../../../include/pbrtgpu.h"
 #include "bvh.h"
+#include "lights.h"
 
 namespace pg {
 
@@ -111,6 +112,83 @@ inline bool buildTris(const pbrtgpu_scene *s, std::vector<F4> *out, std::string 
             tris[3 * last].w = i2f(tag | kTagLast);
         }
     return true;
+}
+
+// InfiniteAreaLight's constructor for a constant light (lights/infinite.cpp:43-82):
+// a 1x1 Lmap, a 2x2 scalar image of Lmap->Lookup(st, fwidth).y() * sinTheta and its
+// Distribution2D (core/sampling.h:55-70, sampling.cpp Distribution2D ctor).
+// Stored into the spare floats of the light record (layout: lights_eval.h).
+inline void finishInfiniteLight(float *lp) {
+    const int width = 2, height = 2;
+    float img[4];
+    for (int v = 0; v < height; ++v) {
+        float vp = (v + .5f) / (float)height;
+        float sinTheta = std::sin(kPi * (v + .5f) / height);
+        for (int u = 0; u < width; ++u) {
+            float up = (u + .5f) / (float)width;
+            Spec t = infiniteLookup(spec(lp[0], lp[1], lp[2]), up, vp);  // MIPMap::Lookup(st, 0.25) -> level < 0 -> triangle(0, st)
+            img[u + v * width] = luminance(t);
+            img[u + v * width] *= sinTheta;
+        }
+    }
+    auto dist1D = [](const float *func, int n, float *cdf, float *funcInt) {
+        cdf[0] = 0;
+        for (int i = 1; i < n + 1; ++i) cdf[i] = cdf[i - 1] + func[i - 1] / n;
+        *funcInt = cdf[n];
+        if (*funcInt == 0)
+            for (int i = 1; i < n + 1; ++i) cdf[i] = float(i) / float(n);
+        else
+            for (int i = 1; i < n + 1; ++i) cdf[i] /= *funcInt;
+    };
+    float marginalFunc[2];
+    for (int v = 0; v < height; ++v) {
+        float cdf[3], funcInt;
+        dist1D(&img[v * width], width, cdf, &funcInt);
+        float *row = lp + kInfRow + 4 * v;
+        row[0] = img[v * width], row[1] = img[v * width + 1], row[2] = cdf[1], row[3] = funcInt;
+        marginalFunc[v] = funcInt;
+    }
+    float cdf[3], funcInt;
+    dist1D(marginalFunc, height, cdf, &funcInt);
+    lp[kInfMargCdf] = cdf[1];
+    lp[kInfMargInt] = funcInt;
+}
+
+
+// PathIntegrator::Preprocess -> CreateLightSampleDistribution (core/lightdistrib.cpp:48-66,
+// 68-88; ComputeLightPowerDistribution core/integrator.cpp:44-50): the
+// Distribution1D the light is picked from.  strategy 0 = uniform, 1 = power.
+inline void buildLightDistribution(const pbrtgpu_scene *s, int strategy, std::vector<float> *func, std::vector<float> *cdf,
+                                   float *funcInt) {
+    int n = s->n_lights;
+    func->assign(n > 0 ? n : 1, 1.f);
+    if (strategy == 1 && n > 1) {
+        for (int i = 0; i < n; ++i) {
+            const float *lp = s->light_params + (size_t)i * PBRTGPU_LIGHT_STRIDE;
+            Spec L = spec(lp[0], lp[1], lp[2]), P;
+            float R = s->world_radius;
+            switch (s->light_tag[i]) {
+            case PBRTGPU_LIGHT_DIFFUSE_AREA:
+            case PBRTGPU_LIGHT_PORTAL_AREA: P = (lp[3] != 0.f ? 2 : 1) * L * lp[4] * kPi; break;  // diffuse.cpp:65-67
+            case PBRTGPU_LIGHT_INFINITE: P = kPi * R * R * infiniteLookup(L, .5f, .5f); break;    // infinite.cpp:86-90
+            case PBRTGPU_LIGHT_POINT: P = 4 * kPi * L; break;                                     // point.cpp:57
+            default: P = L * kPi * R * R; break;                                                  // distant.cpp:65-67
+            }
+            (*func)[i] = luminance(P);
+        }
+    }
+    cdf->assign(n + 1 > 1 ? n + 1 : 2, 0.f);
+    if (n == 0) {
+        *funcInt = 0;
+        return;
+    }
+    (*cdf)[0] = 0;
+    for (int i = 1; i < n + 1; ++i) (*cdf)[i] = (*cdf)[i - 1] + (*func)[i - 1] / n;
+    *funcInt = (*cdf)[n];
+    if (*funcInt == 0)
+        for (int i = 1; i < n + 1; ++i) (*cdf)[i] = float(i) / float(n);
+    else
+        for (int i = 1; i < n + 1; ++i) (*cdf)[i] /= *funcInt;
 }
 
 }  // namespace pg

@@ -1,0 +1,147 @@
+// The wavefront path integrator: SamplerIntegrator::Render + PathIntegrator::Li
+// (core/integrator.cpp:526-637, integrators/path.cpp:64-189) as a sequence of
+// kernels over queues of path vertices.  Per batch of paths:
+//
+//   k_raygen                       camera samples -> closest-hit queue 0
+//   for depth = 0 .. maxDepth:
+//     k_trace_closest              BVHAccel::Intersect for the queue
+//     k_shade                      emission, BSDF, next-event ray generation, BSDF sampling,
+//                                  Russian roulette; survivors are compacted into the other queue
+//     k_trace_shadow               BVHAccel::IntersectP for the light samples, resolved in place
+//     k_trace_nee                  BVHAccel::Intersect for BSDF-sampled / portal rays, resolved in place
+//   k_film                         scrub + FilmTile::AddSample (float atomics)
+//
+// Queue lengths live in device memory (WaveCounters): no kernel's launch
+// geometry depends on them, so a batch runs without a single host sync.
+// The stage bodies are in integrator.h; this file only maps threads to entries.
+#include <algorithm>
+#include <cstdlib>
+#include <cstring>
+
+#include "../common/halton_tables.h"
+#include "ctx.h"
+#include "integrator.h"
+#include "kernels.h"
+
+using namespace pg;
+
+namespace pg {
+
+constexpr int kStageBlock = 128;
+
+__global__ void __launch_bounds__(kStageBlock) k_raygen(WaveParams w) {
+    int stride = gridDim.x * blockDim.x;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < w.nSlots; i += stride) stageRaygen(w, i);
+}
+
+__global__ void __launch_bounds__(kTraceBlock) k_trace_closest(WaveParams w, int depth, int cur) {
+    int n = w.cnt->nActive[depth];
+    int stride = gridDim.x * blockDim.x;
+    const F4 *rays = w.rays[cur];
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        Ray ray = loadRay(rays, i);
+        Hit h;
+        traverse<false>(w.sc.bvh, ray, &h);
+        w.hits[i] = f4(__int_as_float(h.prim), h.b0, h.b1, h.b2);
+    }
+}
+
+__global__ void __launch_bounds__(kStageBlock) k_shade(WaveParams w, int depth, int cur) {
+    int n = w.cnt->nActive[depth];
+    int stride = gridDim.x * blockDim.x;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) stageShade(w, depth, cur, i);
+}
+
+__global__ void __launch_bounds__(kTraceBlock) k_trace_shadow(WaveParams w, int depth) {
+    int n = w.cnt->nShadow[depth];
+    int stride = gridDim.x * blockDim.x;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        Ray ray = loadRay(w.shadowRays, i);
+        bool occ = traverse<true>(w.sc.bvh, ray, nullptr);
+        stageShadowResolve(w, i, occ);
+    }
+}
+
+__global__ void __launch_bounds__(kTraceBlock) k_trace_nee(WaveParams w, int depth) {
+    int n = w.cnt->nNee[depth];
+    int stride = gridDim.x * blockDim.x;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        Ray ray = loadRay(w.neeRays, i);
+        Hit h;
+        traverse<false>(w.sc.bvh, ray, &h);
+        w.neeHits[i] = f4(__int_as_float(h.prim), h.b0, h.b1, h.b2);
+        stageNeeResolve(w, i);
+    }
+}
+
+__global__ void __launch_bounds__(kStageBlock) k_film(WaveParams w) {
+    int stride = gridDim.x * blockDim.x;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < w.nSlots; i += stride) stageFilm(w, i);
+}
+
+// fold one batch's counters into the running totals, then clear them for the next batch
+__global__ void k_batch_stats(WaveCounters *cnt, unsigned long long *totals, int depths) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    unsigned long long closest = 0, shadow = 0;
+    for (int d = 0; d <= depths; ++d) closest += (unsigned long long)cnt->nActive[d];
+    for (int d = 0; d < depths; ++d) closest += (unsigned long long)cnt->nNee[d], shadow += (unsigned long long)cnt->nShadow[d];
+    totals[0] += (unsigned long long)cnt->nActive[0];
+    totals[1] += closest;
+    totals[2] += shadow;
+    totals[3] += cnt->scrubbed;
+    for (int d = 0; d <= kMaxDepthSlots; ++d) cnt->nActive[d] = 0;
+    for (int d = 0; d < kMaxDepthSlots; ++d) cnt->nShadow[d] = cnt->nNee[d] = 0;
+    cnt->scrubbed = 0;
+}
+
+// Film::MergeFilmTile's RGB -> XYZ (film.cpp:125-127), once per pixel at the end
+__global__ void k_film_to_xyz(float *rgbw, long long nPixels) {
+    long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nPixels; i += stride) {
+        float4 v = reinterpret_cast<float4 *>(rgbw)[i];
+        float rgb[3] = {v.x, v.y, v.z}, xyz[3];
+        rgbToXYZ(rgb, xyz);
+        reinterpret_cast<float4 *>(rgbw)[i] = make_float4(xyz[0], xyz[1], xyz[2], v.w);
+    }
+}
+
+// HaltonSampler::SampleDimension on a batch, for unit parity against the oracle
+__global__ void k_halton(HaltonParams h, const int *pixelXY, const long long *sampleNum, const int *dim, long long n, float *out) {
+    long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        long long index = haltonPixelOffset(h, pixelXY[2 * i], pixelXY[2 * i + 1]) + sampleNum[i] * h.sampleStride;
+        out[i] = haltonSample(h, index, dim[i]);
+    }
+}
+
+}  // namespace pg
+
+#include "render_host.inc"
+
+extern "C" int pbrtgpu_halton_samples(pbrtgpu_ctx *ctx, const pbrtgpu_render_params *params, const int32_t *pixel_xy,
+                                      const int64_t *sample_num, const int32_t *dim, int64_t n, float *out) {
+    if (!ctx || !params || (n > 0 && (!pixel_xy || !sample_num || !dim || !out))) return PBRTGPU_ERR_INVALID;
+    if (n <= 0) return PBRTGPU_OK;
+    for (int64_t i = 0; i < n; ++i)
+        if (dim[i] < 0 || dim[i] >= kPrimeTableSize) return ctx->fail(PBRTGPU_ERR_INVALID, "HaltonSampler can only sample %d dimensions.", kPrimeTableSize);
+    PG_CUDA(ctx, cudaSetDevice(ctx->device));
+    HaltonParams h = makeHaltonParams(params->sample_bounds, params->sample_at_pixel_center);
+    h.primes = ctx->dPrimes, h.primeSums = ctx->dPrimeSums, h.perms = ctx->dPerms;
+    int rc;
+    size_t bytes = (size_t)n * (8 + 8 + 4 + 4);
+    if ((rc = ensureBuffer(ctx, ctx->scratch[2], bytes)) != PBRTGPU_OK) return rc;
+    char *base = (char *)ctx->scratch[2].p;
+    long long *dNum = (long long *)base;
+    int *dXY = (int *)(base + 8 * (size_t)n);
+    int *dDim = (int *)(base + 16 * (size_t)n);
+    float *dOut = (float *)(base + 20 * (size_t)n);
+    PG_CUDA(ctx, cudaMemcpyAsync(dNum, sample_num, 8 * (size_t)n, cudaMemcpyHostToDevice, ctx->stream));
+    PG_CUDA(ctx, cudaMemcpyAsync(dXY, pixel_xy, 8 * (size_t)n, cudaMemcpyHostToDevice, ctx->stream));
+    PG_CUDA(ctx, cudaMemcpyAsync(dDim, dim, 4 * (size_t)n, cudaMemcpyHostToDevice, ctx->stream));
+    k_halton<<<stageGrid(ctx, n, 128, 8), 128, 0, ctx->stream>>>(h, dXY, dNum, dDim, n, dOut);
+    ctx->launches++;
+    PG_CUDA(ctx, cudaGetLastError());
+    PG_CUDA(ctx, cudaMemcpyAsync(out, dOut, 4 * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
+    PG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return PBRTGPU_OK;
+}

@@ -1,0 +1,181 @@
+// Halton sampler on the device: a pure function of (pixel, sample number,
+// dimension), exactly the stream the reference's HaltonSampler hands to
+// PathIntegrator::Li.
+//   HaltonSampler ctor / GetIndexForSample / SampleDimension   samplers/halton.cpp:65-127
+//   GlobalSampler::Get1D / Get2D                                core/sampler.cpp:181-196
+//   RadicalInverse / ScrambledRadicalInverse                    core/lowdiscrepancy.cpp:390-433, 2506-
+//   InverseRadicalInverse                                       core/lowdiscrepancy.h:83-91
+// The reference unrolls one radical inverse per prime base with a compile-time
+// divisor; here the base comes from a table and the quotient is taken with a
+// 32-bit divide whenever the running index fits (it does for every BASELINE
+// config: stride 31104 x 4096 spp < 2^32), which yields the same digits.
+#ifndef PG_DEVICE_SAMPLER_H
+#define PG_DEVICE_SAMPLER_H
+
+#include "../common/pg_math.h"
+
+namespace pg {
+
+constexpr int kHaltonMaxResolution = 128;  // halton.cpp:42
+
+struct HaltonParams {
+    int baseScales[2], baseExponents[2];
+    int sampleStride;
+    int multInverse[2];
+    int sampleAtPixelCenter;
+    const int *primes;             // 1000 entries
+    const int *primeSums;          // 1000 entries
+    const unsigned short *perms;   // 3,682,913 entries
+};
+
+PG_HD int modPos(int a, int b) {  // Mod(), pbrt.h
+    int r = a - (a / b) * b;
+    return r < 0 ? r + b : r;
+}
+
+// GetIndexForSample(0) for a pixel: the CRT offset of the pixel inside the
+// 128-pixel Halton tile (halton.cpp:96-116).
+PG_HD long long haltonPixelOffset(const HaltonParams &h, int px, int py) {
+    unsigned long long offset = 0;
+    if (h.sampleStride > 1) {
+        int pm[2] = {modPos(px, kHaltonMaxResolution), modPos(py, kHaltonMaxResolution)};
+        for (int i = 0; i < 2; ++i) {
+            unsigned base = i == 0 ? 2u : 3u;
+            unsigned inverse = (unsigned)pm[i], index = 0;
+            for (int k = 0; k < h.baseExponents[i]; ++k) {
+                unsigned digit = inverse % base;
+                inverse /= base;
+                index = index * base + digit;
+            }
+            offset += (unsigned long long)index * (unsigned long long)(h.sampleStride / h.baseScales[i]) *
+                      (unsigned long long)h.multInverse[i];
+        }
+        offset %= (unsigned long long)h.sampleStride;
+    }
+    return (long long)offset;
+}
+
+PG_HD unsigned long long reverseBits64(unsigned long long n) {
+#if defined(__CUDA_ARCH__)
+    return __brevll(n);
+#else
+    unsigned long long r = 0;
+    for (int i = 0; i < 64; ++i) r |= ((n >> i) & 1ull) << (63 - i);
+    return r;
+#endif
+}
+
+// RadicalInverseSpecialized<base>, lowdiscrepancy.cpp:390-404
+PG_HD float radicalInverseBase(unsigned base, unsigned long long a) {
+    const float invBase = (float)1 / (float)base;
+    unsigned long long reversedDigits = 0;
+    float invBaseN = 1;
+    while (a > 0xffffffffull) {
+        unsigned long long next = a / base;
+        unsigned long long digit = a - next * base;
+        reversedDigits = reversedDigits * base + digit;
+        invBaseN *= invBase;
+        a = next;
+    }
+    unsigned a32 = (unsigned)a;
+    while (a32) {
+        unsigned next = a32 / base;
+        unsigned digit = a32 - next * base;
+        reversedDigits = reversedDigits * base + digit;
+        invBaseN *= invBase;
+        a32 = next;
+    }
+    return minf((float)reversedDigits * invBaseN, kOneMinusEpsilon);
+}
+
+// ScrambledRadicalInverseSpecialized<base>, lowdiscrepancy.cpp:406-423
+PG_HD float scrambledRadicalInverseBase(unsigned base, const unsigned short *perm, unsigned long long a) {
+    const float invBase = (float)1 / (float)base;
+    unsigned long long reversedDigits = 0;
+    float invBaseN = 1;
+    while (a > 0xffffffffull) {
+        unsigned long long next = a / base;
+        unsigned long long digit = a - next * base;
+        reversedDigits = reversedDigits * base + PG_LD(perm + digit);
+        invBaseN *= invBase;
+        a = next;
+    }
+    unsigned a32 = (unsigned)a;
+    while (a32) {
+        unsigned next = a32 / base;
+        unsigned digit = a32 - next * base;
+        reversedDigits = reversedDigits * base + PG_LD(perm + digit);
+        invBaseN *= invBase;
+        a32 = next;
+    }
+    return minf(invBaseN * ((float)reversedDigits + invBase * (float)PG_LD(perm) / (1 - invBase)), kOneMinusEpsilon);
+}
+
+// HaltonSampler::SampleDimension, halton.cpp:118-127
+PG_HD float haltonSample(const HaltonParams &h, long long index, int dim) {
+    if (h.sampleAtPixelCenter && (dim == 0 || dim == 1)) return 0.5f;
+    if (dim == 0) {
+        unsigned long long a = (unsigned long long)(index >> h.baseExponents[0]);
+        return (float)((double)reverseBits64(a) * 0x1p-64);  // RadicalInverse case 0
+    }
+    if (dim == 1) return radicalInverseBase(3u, (unsigned long long)(index / h.baseScales[1]));
+    unsigned base = (unsigned)PG_LD(h.primes + dim);
+    return scrambledRadicalInverseBase(base, h.perms + PG_LD(h.primeSums + dim), (unsigned long long)index);
+}
+
+// HaltonSampler's constructor (halton.cpp:65-93): scales/exponents that cover
+// min(resolution, 128) in bases 2 and 3, the stride and the CRT inverses.
+// Host side; the table pointers are filled in by the caller.
+inline void haltonExtendedGCD(unsigned long long a, unsigned long long b, long long *x, long long *y) {
+    if (b == 0) {
+        *x = 1;
+        *y = 0;
+        return;
+    }
+    long long d = (long long)(a / b), xp, yp;
+    haltonExtendedGCD(b, a % b, &xp, &yp);
+    *x = yp;
+    *y = xp - (d * yp);
+}
+inline HaltonParams makeHaltonParams(const int sampleBounds[4], int sampleAtPixelCenter) {
+    HaltonParams h;
+    int res[2] = {sampleBounds[2] - sampleBounds[0], sampleBounds[3] - sampleBounds[1]};
+    for (int i = 0; i < 2; ++i) {
+        int base = (i == 0) ? 2 : 3;
+        int scale = 1, exp = 0;
+        int lim = res[i] < kHaltonMaxResolution ? res[i] : kHaltonMaxResolution;
+        while (scale < lim) {
+            scale *= base;
+            ++exp;
+        }
+        h.baseScales[i] = scale;
+        h.baseExponents[i] = exp;
+    }
+    h.sampleStride = h.baseScales[0] * h.baseScales[1];
+    for (int i = 0; i < 2; ++i) {
+        long long x, y, n = h.baseScales[i];
+        haltonExtendedGCD((unsigned long long)h.baseScales[1 - i], (unsigned long long)n, &x, &y);
+        long long m = x - (x / n) * n;  // Mod(x, n)
+        h.multInverse[i] = (int)(m < 0 ? m + n : m);
+    }
+    h.sampleAtPixelCenter = sampleAtPixelCenter;
+    h.primes = nullptr;
+    h.primeSums = nullptr;
+    h.perms = nullptr;
+    return h;
+}
+
+// The per-path view of GlobalSampler: interval sample index + running dimension.
+struct PathSampler {
+    long long index;
+    int dim;
+};
+PG_HD float get1D(const HaltonParams &h, PathSampler &s) { return haltonSample(h, s.index, s.dim++); }
+PG_HD void get2D(const HaltonParams &h, PathSampler &s, float *u0, float *u1) {
+    *u0 = haltonSample(h, s.index, s.dim);
+    *u1 = haltonSample(h, s.index, s.dim + 1);
+    s.dim += 2;
+}
+
+}  // namespace pg
+#endif

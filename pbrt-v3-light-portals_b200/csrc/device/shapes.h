@@ -17,7 +17,7 @@ struct Ray {
 // ---- Triangle::Intersect / IntersectP test part, shapes/triangle.cpp:199-292
 // (identical in 427-520).  Returns true when the hit is accepted for
 // ray.tMax; does not update tMax.
-PG_HD bool triangleTest(const Ray &ray, V3 p0, V3 p1, V3 p2, float *tOut, float *b0Out, float *b1Out) {
+PG_HD bool triangleTest(const Ray &ray, V3 p0, V3 p1, V3 p2, float *tOut, float *b0Out, float *b1Out, float *b2Out = nullptr) {
     V3 p0t = p0 - ray.o, p1t = p1 - ray.o, p2t = p2 - ray.o;
     int kz = maxDimension(vabs(ray.d));
     int kx = kz + 1;
@@ -59,7 +59,7 @@ PG_HD bool triangleTest(const Ray &ray, V3 p0, V3 p1, V3 p2, float *tOut, float 
     if (det < 0 && (tScaled >= 0 || tScaled < ray.tMax * det)) return false;
     else if (det > 0 && (tScaled <= 0 || tScaled > ray.tMax * det)) return false;
     float invDet = 1 / det;
-    float b0 = e0 * invDet, b1 = e1 * invDet;
+    float b0 = e0 * invDet, b1 = e1 * invDet, b2 = e2 * invDet;
     float t = tScaled * invDet;
     // conservative t > 0 check, triangle.cpp:271-292
     float maxZt = maxComponent(vabs(v3(p0t.z, p1t.z, p2t.z)));
@@ -75,6 +75,7 @@ PG_HD bool triangleTest(const Ray &ray, V3 p0, V3 p1, V3 p2, float *tOut, float 
     *tOut = t;
     *b0Out = b0;
     *b1Out = b1;
+    if (b2Out) *b2Out = b2;
     return true;
 }
 

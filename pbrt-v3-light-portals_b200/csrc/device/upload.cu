@@ -65,6 +65,16 @@ int pbrtgpu_create(int cuda_device, pbrtgpu_ctx **out) {
     if ((e = cudaMalloc((void **)&ctx->dPerms, perms.size() * sizeof(uint16_t))) != cudaSuccess) return bail(e, "cudaMalloc(perms)");
     if ((e = cudaMemcpy(ctx->dPerms, perms.data(), perms.size() * sizeof(uint16_t), cudaMemcpyHostToDevice)) != cudaSuccess)
         return bail(e, "cudaMemcpy(perms)");
+    {
+        std::vector<int> primes = firstPrimes(), sums(primes.size());
+        int acc = 0;
+        for (size_t i = 0; i < primes.size(); ++i) sums[i] = acc, acc += primes[i];
+        if ((e = cudaMalloc((void **)&ctx->dPrimes, primes.size() * sizeof(int))) != cudaSuccess) return bail(e, "cudaMalloc(primes)");
+        if ((e = cudaMalloc((void **)&ctx->dPrimeSums, primes.size() * sizeof(int))) != cudaSuccess) return bail(e, "cudaMalloc(primeSums)");
+        if ((e = cudaMalloc((void **)&ctx->dTotals, 4 * sizeof(unsigned long long))) != cudaSuccess) return bail(e, "cudaMalloc(totals)");
+        cudaMemcpy(ctx->dPrimes, primes.data(), primes.size() * sizeof(int), cudaMemcpyHostToDevice);
+        cudaMemcpy(ctx->dPrimeSums, sums.data(), primes.size() * sizeof(int), cudaMemcpyHostToDevice);
+    }
     *out = ctx;
     return PBRTGPU_OK;
 }
@@ -77,6 +87,13 @@ void pbrtgpu_destroy(pbrtgpu_ctx *ctx) {
         if (b.p) cudaFree(b.p);
     if (ctx->film.p) cudaFree(ctx->film.p);
     if (ctx->dPerms) cudaFree(ctx->dPerms);
+    if (ctx->dPrimes) cudaFree(ctx->dPrimes);
+    if (ctx->dPrimeSums) cudaFree(ctx->dPrimeSums);
+    if (ctx->dTotals) cudaFree(ctx->dTotals);
+    for (auto &b : ctx->wave)
+        if (b.p) cudaFree(b.p);
+    if (ctx->lightDist.p) cudaFree(ctx->lightDist.p);
+    if (ctx->filterTable.p) cudaFree(ctx->filterTable.p);
     if (ctx->ownStream && ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -138,9 +155,29 @@ int pbrtgpu_upload_scene(pbrtgpu_ctx *ctx, const pbrtgpu_scene *s) {
     UP(s->light_prim, s->n_lights, &d.lightPrim);
     UP(s->light_strategy, s->n_lights, &d.lightStrategy);
     UP(s->light_portal_begin, s->light_portal_begin ? s->n_lights + 1 : 0, &d.lightPortalBegin);
-    UP(s->light_params, (size_t)s->n_lights * PBRTGPU_LIGHT_STRIDE, &d.lightParams);
+    std::vector<float> lightParams(s->light_params, s->light_params + (size_t)s->n_lights * PBRTGPU_LIGHT_STRIDE);
+    for (int i = 0; i < s->n_lights; ++i)
+        if (s->light_tag[i] == PBRTGPU_LIGHT_INFINITE) finishInfiniteLight(lightParams.data() + (size_t)i * PBRTGPU_LIGHT_STRIDE);
+    UP(lightParams.data(), lightParams.size(), &d.lightParams);
+    ctx->hasNullMaterial = false;
+    if (s->prim_material)
+        for (int i = 0; i < s->n_prims; ++i)
+            if (s->prim_material[i] < 0) ctx->hasNullMaterial = true;
     UP(s->portal_params, (size_t)s->n_portals * PBRTGPU_PORTAL_STRIDE, &d.portalParams);
 #undef UP
+    {   // light-pick distributions for both "lightsamplestrategy" values (uniform, power)
+        std::vector<float> all;
+        for (int strategy = 0; strategy < 2; ++strategy) {
+            std::vector<float> func, cdf;
+            pbrtgpu_scene tmp = *s;
+            tmp.light_params = lightParams.data();
+            buildLightDistribution(&tmp, strategy, &func, &cdf, &ctx->lightFuncInt[strategy]);
+            all.insert(all.end(), func.begin(), func.end());
+            all.insert(all.end(), cdf.begin(), cdf.end());
+        }
+        if ((rc = ensureBuffer(ctx, ctx->lightDist, all.size() * sizeof(float))) != PBRTGPU_OK) return rc;
+        PG_CUDA(ctx, cudaMemcpy(ctx->lightDist.p, all.data(), all.size() * sizeof(float), cudaMemcpyHostToDevice));
+    }
     memcpy(d.worldCenter, s->world_center, sizeof(d.worldCenter));
     d.worldRadius = s->world_radius;
     PG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));

@@ -1,0 +1,103 @@
+// Host-side setup shared by the CUDA driver (render.cu) and tests/hostsim:
+// pbrtgpu_render_params -> the value part of WaveParams, the batch plan, and
+// the per-slot buffer table.  Plain C++.
+#ifndef PG_DEVICE_WAVE_SETUP_H
+#define PG_DEVICE_WAVE_SETUP_H
+
+#include <cstring>
+
+#include "../../../include/pbrtgpu.h"
+#include "integrator.h"
+
+namespace pg {
+
+inline void fillWaveParams(const pbrtgpu_render_params *rp, WaveParams *w) {
+    memcpy(w->cam.cameraToWorld.m, rp->camera_to_world, 64);
+    memcpy(w->cam.rasterToCamera.m, rp->raster_to_camera, 64);
+    w->cam.lensRadius = rp->lens_radius;
+    w->cam.focalDistance = rp->focal_distance;
+    for (int i = 0; i < 4; ++i) {
+        w->film.cropped[i] = rp->cropped_bounds[i];
+        w->film.sampleBounds[i] = rp->sample_bounds[i];
+        w->film.pixelBounds[i] = rp->pixel_bounds[i];
+    }
+    for (int i = 0; i < 2; ++i) {
+        w->film.radius[i] = rp->filter_radius[i];
+        w->film.invRadius[i] = 1 / rp->filter_radius[i];  // FilmTile: invFilterRadius(1 / filterRadius.x, ...)
+    }
+    w->film.maxSampleLuminance = rp->max_sample_luminance;
+    w->hal = makeHaltonParams(rp->sample_bounds, rp->sample_at_pixel_center);
+    w->maxDepth = rp->max_depth;
+    w->rrThreshold = rp->rr_threshold;
+    int sw = rp->sample_bounds[2] - rp->sample_bounds[0];
+    w->tilesX = (sw + 15) / 16;
+    w->shardIndex = rp->shard_index;
+    w->shardCount = rp->shard_count > 0 ? rp->shard_count : 1;
+}
+
+struct BatchPlan {
+    int tilesX, tilesY, shardTiles;  // shardTiles = tiles t with t % shardCount == shardIndex
+    int sppBegin, sppEnd;
+    int sppChunk;        // samples of a pixel per batch
+    int tilesPerBatch;
+    int maxSlots;
+    int depthIters;      // wavefront iterations per batch
+};
+
+inline BatchPlan planBatches(const pbrtgpu_render_params *rp, long long targetSlots, bool hasNullMaterial) {
+    BatchPlan p;
+    int sw = rp->sample_bounds[2] - rp->sample_bounds[0], sh = rp->sample_bounds[3] - rp->sample_bounds[1];
+    p.tilesX = (sw + 15) / 16;
+    p.tilesY = (sh + 15) / 16;
+    int total = p.tilesX * p.tilesY;
+    int sc = rp->shard_count > 0 ? rp->shard_count : 1;
+    p.shardTiles = total > rp->shard_index ? (total - rp->shard_index + sc - 1) / sc : 0;
+    p.sppBegin = rp->spp_begin;
+    p.sppEnd = rp->spp_end > rp->spp_begin ? rp->spp_end : rp->spp;
+    int spp = p.sppEnd - p.sppBegin;
+    p.sppChunk = spp < 32 ? (spp > 0 ? spp : 1) : 32;
+    long long t = targetSlots / (256LL * p.sppChunk);
+    if (t < 1) t = 1;
+    if (t > p.shardTiles) t = p.shardTiles > 0 ? p.shardTiles : 1;
+    p.tilesPerBatch = (int)t;
+    p.maxSlots = p.tilesPerBatch * 256 * p.sppChunk;
+    // a path makes at most maxDepth + 1 scene intersections; vertices on
+    // material-less primitives do not count as bounces (path.cpp:108-113), so
+    // leave room for a few of those when the scene has any
+    p.depthIters = rp->max_depth + 1 + (hasNullMaterial ? 8 : 0);
+    if (p.depthIters > kMaxDepthSlots) p.depthIters = kMaxDepthSlots;
+    return p;
+}
+
+// Bytes per slot of each wave buffer, in the order render.cu / hostsim bind them.
+enum WaveBuf {
+    WB_HINDEX, WB_DIM, WB_L, WB_BETA, WB_FLAGS, WB_PFILM, WB_RAYS0, WB_RAYS1, WB_Q0, WB_Q1, WB_HITS, WB_SHADOW_RAYS,
+    WB_SHADOW_CONTRIB, WB_NEE_RAYS, WB_NEE_CONTRIB, WB_NEE_INFO, WB_NEE_HITS, WB_SHADOW_OCC, WB_COUNT
+};
+inline size_t waveBufBytesPerSlot(int b) {
+    static const size_t sz[WB_COUNT] = {8, 4, 16, 16, 4, 8, 32, 32, 4, 4, 16, 32, 16, 32, 16, 8, 16, 1};
+    return sz[b];
+}
+inline void bindWaveBuffers(WaveParams *w, void *const bufs[WB_COUNT]) {
+    w->hIndex = (long long *)bufs[WB_HINDEX];
+    w->dim = (int *)bufs[WB_DIM];
+    w->L = (F4 *)bufs[WB_L];
+    w->beta = (F4 *)bufs[WB_BETA];
+    w->flags = (int *)bufs[WB_FLAGS];
+    w->pFilm = (float *)bufs[WB_PFILM];
+    w->rays[0] = (F4 *)bufs[WB_RAYS0];
+    w->rays[1] = (F4 *)bufs[WB_RAYS1];
+    w->qSlot[0] = (int *)bufs[WB_Q0];
+    w->qSlot[1] = (int *)bufs[WB_Q1];
+    w->hits = (F4 *)bufs[WB_HITS];
+    w->shadowRays = (F4 *)bufs[WB_SHADOW_RAYS];
+    w->shadowContrib = (F4 *)bufs[WB_SHADOW_CONTRIB];
+    w->neeRays = (F4 *)bufs[WB_NEE_RAYS];
+    w->neeContrib = (F4 *)bufs[WB_NEE_CONTRIB];
+    w->neeInfo = (int *)bufs[WB_NEE_INFO];
+    w->neeHits = (F4 *)bufs[WB_NEE_HITS];
+    w->shadowOcc = (unsigned char *)bufs[WB_SHADOW_OCC];
+}
+
+}  // namespace pg
+#endif

@@ -84,3 +84,131 @@ int hostsim_intersect_any(void *p, const float *rays, int64_t n, uint8_t *occ, i
 }
 
 }  // extern "C"
+
+// ---- the wavefront path integrator, stepped on the CPU (same stage functions
+// as render.cu's kernels, same batch plan, same buffers)
+#include "../../pbrt-v3-light-portals_b200/csrc/common/halton_tables.h"
+#include "../../pbrt-v3-light-portals_b200/csrc/device/wave_setup.h"
+
+extern "C" int hostsim_render(void *p, const pbrtgpu_render_params *rp, float *film_xyzw, int64_t *stats4, int threads) {
+    SimScene *sim = (SimScene *)p;
+    const pbrtgpu_scene *s = sim->src;
+    DevScene sc;
+    memset(&sc, 0, sizeof(sc));
+    sc.bvh = sim->bvh;
+    sc.nPrims = s->n_prims, sc.nLights = s->n_lights, sc.nMaterials = s->n_materials;
+    sc.primOrigId = s->prim_orig_id, sc.primMaterial = s->prim_material, sc.primLight = s->prim_light;
+    sc.primFlags = s->prim_flags, sc.triN = s->tri_n, sc.triUV = s->tri_uv, sc.triS = s->tri_s;
+    sc.matTag = s->mat_tag, sc.matParams = s->mat_params;
+    sc.lightTag = s->light_tag, sc.lightPrim = s->light_prim, sc.lightStrategy = s->light_strategy;
+    sc.lightPortalBegin = s->light_portal_begin, sc.portalParams = s->portal_params;
+    std::vector<float> lightParams(s->light_params, s->light_params + (size_t)s->n_lights * PBRTGPU_LIGHT_STRIDE);
+    for (int i = 0; i < s->n_lights; ++i)
+        if (s->light_tag[i] == PBRTGPU_LIGHT_INFINITE) finishInfiniteLight(lightParams.data() + (size_t)i * PBRTGPU_LIGHT_STRIDE);
+    sc.lightParams = lightParams.data();
+    std::vector<float> lfunc, lcdf;
+    pbrtgpu_scene tmp = *s;
+    tmp.light_params = lightParams.data();
+    buildLightDistribution(&tmp, (rp->light_strategy == 1 && s->n_lights > 1) ? 1 : 0, &lfunc, &lcdf, &sc.lightFuncInt);
+    sc.lightFunc = lfunc.data(), sc.lightCdf = lcdf.data();
+    memcpy(sc.worldCenter, s->world_center, 12);
+    sc.worldRadius = s->world_radius;
+    bool nullMat = false;
+    if (s->prim_material)
+        for (int i = 0; i < s->n_prims; ++i) nullMat |= s->prim_material[i] < 0;
+
+    std::vector<int> primes = firstPrimes(), sums(primes.size());
+    int acc = 0;
+    for (size_t i = 0; i < primes.size(); ++i) sums[i] = acc, acc += primes[i];
+    std::vector<uint16_t> perms = radicalInversePermutations(primes);
+
+    WaveParams w;
+    memset(&w, 0, sizeof(w));
+    fillWaveParams(rp, &w);
+    w.sc = sc;
+    w.hal.primes = primes.data(), w.hal.primeSums = sums.data(), w.hal.perms = perms.data();
+    BatchPlan pl = planBatches(rp, 1 << 18, nullMat);
+    const int *cb = rp->cropped_bounds;
+    size_t nPix = (size_t)(cb[2] - cb[0]) * (cb[3] - cb[1]);
+    std::vector<float> film(nPix * 4, 0.f);
+    w.film.rgbw = film.data();
+    w.film.filterTable = rp->filter_table;
+    std::vector<std::vector<char>> store(WB_COUNT);
+    void *bufs[WB_COUNT];
+    for (int b = 0; b < WB_COUNT; ++b) {
+        store[b].resize(waveBufBytesPerSlot(b) * (size_t)pl.maxSlots + 16);
+        bufs[b] = store[b].data();
+    }
+    bindWaveBuffers(&w, bufs);
+    WaveCounters cnt;
+    w.cnt = &cnt;
+    int64_t totals[4] = {0, 0, 0, 0};
+    for (int s0 = pl.sppBegin; s0 < pl.sppEnd; s0 += pl.sppChunk) {
+        w.sppBegin = s0;
+        w.sppCount = std::min(pl.sppChunk, pl.sppEnd - s0);
+        for (int t0 = 0; t0 < pl.shardTiles; t0 += pl.tilesPerBatch) {
+            int nt = std::min(pl.tilesPerBatch, pl.shardTiles - t0);
+            w.tileBegin = t0;
+            w.nSlots = nt * 256 * w.sppCount;
+            memset(&cnt, 0, sizeof(cnt));
+            parallelFor(w.nSlots, threads, [&](int64_t a, int64_t b) { for (int64_t i = a; i < b; ++i) stageRaygen(w, (int)i); });
+            int cur = 0;
+            for (int d = 0; d < pl.depthIters; ++d) {
+                int n = cnt.nActive[d];
+                parallelFor(n, threads, [&](int64_t a, int64_t b) {
+                    for (int64_t i = a; i < b; ++i) {
+                        Ray ray = loadRay(w.rays[cur], (int)i);
+                        Hit h;
+                        traverse<false>(w.sc.bvh, ray, &h);
+                        w.hits[i] = f4(bitsToFloat((unsigned)h.prim), h.b0, h.b1, h.b2);
+                    }
+                });
+                parallelFor(n, threads, [&](int64_t a, int64_t b) { for (int64_t i = a; i < b; ++i) stageShade(w, d, cur, (int)i); });
+                parallelFor(cnt.nShadow[d], threads, [&](int64_t a, int64_t b) {
+                    for (int64_t i = a; i < b; ++i) {
+                        Ray ray = loadRay(w.shadowRays, (int)i);
+                        stageShadowResolve(w, (int)i, traverse<true>(w.sc.bvh, ray, nullptr));
+                    }
+                });
+                parallelFor(cnt.nNee[d], threads, [&](int64_t a, int64_t b) {
+                    for (int64_t i = a; i < b; ++i) {
+                        Ray ray = loadRay(w.neeRays, (int)i);
+                        Hit h;
+                        traverse<false>(w.sc.bvh, ray, &h);
+                        w.neeHits[i] = f4(bitsToFloat((unsigned)h.prim), h.b0, h.b1, h.b2);
+                        stageNeeResolve(w, (int)i);
+                    }
+                });
+                totals[1] += n + cnt.nNee[d];
+                totals[2] += cnt.nShadow[d];
+                cur ^= 1;
+            }
+            parallelFor(w.nSlots, threads, [&](int64_t a, int64_t b) { for (int64_t i = a; i < b; ++i) stageFilm(w, (int)i); });
+            totals[0] += cnt.nActive[0];
+            totals[3] += (int64_t)cnt.scrubbed;
+        }
+    }
+    for (size_t i = 0; i < nPix; ++i) {
+        float xyz[3];
+        rgbToXYZ(&film[4 * i], xyz);
+        film_xyzw[4 * i] = xyz[0], film_xyzw[4 * i + 1] = xyz[1], film_xyzw[4 * i + 2] = xyz[2], film_xyzw[4 * i + 3] = film[4 * i + 3];
+    }
+    if (stats4) memcpy(stats4, totals, sizeof(totals));
+    return 0;
+}
+
+extern "C" int hostsim_halton(const pbrtgpu_render_params *rp, const int32_t *xy, const int64_t *num, const int32_t *dim, int64_t n, float *out) {
+    static std::vector<int> primes = firstPrimes(), sums;
+    static std::vector<uint16_t> perms;
+    if (sums.empty()) {
+        sums.resize(primes.size());
+        int acc = 0;
+        for (size_t i = 0; i < primes.size(); ++i) sums[i] = acc, acc += primes[i];
+        perms = radicalInversePermutations(primes);
+    }
+    HaltonParams h = makeHaltonParams(rp->sample_bounds, rp->sample_at_pixel_center);
+    h.primes = primes.data(), h.primeSums = sums.data(), h.perms = perms.data();
+    for (int64_t i = 0; i < n; ++i)
+        out[i] = haltonSample(h, haltonPixelOffset(h, xy[2 * i], xy[2 * i + 1]) + num[i] * h.sampleStride, dim[i]);
+    return 0;
+}

@@ -156,8 +156,26 @@ typedef struct {
     int64_t shadow_rays;    /* Scene::IntersectP calls (scene.cpp:51) */
     int64_t scrubbed;       /* NaN / negative / infinite samples zeroed (integrator.cpp:592-613) */
     int64_t kernel_launches;
+    int64_t nee_closest_rays; /* the part of closest_rays traced for direct lighting (BSDF-sampled MIS rays, portal rays) */
     float device_ms;        /* CUDA-event time of the render, device only */
 } pbrtgpu_stats;
+
+/* Kernels of the wavefront, for per-kernel timing (pbrtgpu_profile). */
+enum {
+    PBRTGPU_K_RAYGEN = 0,        /* Sampler::GetCameraSample + PerspectiveCamera::GenerateRay */
+    PBRTGPU_K_TRACE_CLOSEST = 1, /* BVHAccel::Intersect for path rays */
+    PBRTGPU_K_SHADE = 2,         /* the body of PathIntegrator::Li for one vertex */
+    PBRTGPU_K_TRACE_SHADOW = 3,  /* BVHAccel::IntersectP for light samples + resolve */
+    PBRTGPU_K_TRACE_NEE = 4,     /* BVHAccel::Intersect for BSDF-sampled / portal rays + resolve */
+    PBRTGPU_K_FILM = 5,          /* FilmTile::AddSample */
+    PBRTGPU_K_COUNT = 6
+};
+typedef struct {
+    double ms[PBRTGPU_K_COUNT];          /* CUDA-event time summed over launches */
+    int64_t launches[PBRTGPU_K_COUNT];
+    int64_t node_tests[PBRTGPU_K_COUNT]; /* Bounds3::IntersectP calls (trace kernels only) */
+    int64_t prim_tests[PBRTGPU_K_COUNT]; /* Shape::Intersect(P) calls (trace kernels only) */
+} pbrtgpu_profile;
 
 int pbrtgpu_abi_version(void);
 int pbrtgpu_create(int cuda_device, pbrtgpu_ctx **out);
@@ -188,6 +206,12 @@ int pbrtgpu_render(pbrtgpu_ctx *ctx, const pbrtgpu_render_params *params,
 /* Same, film left on the device (for the NCCL reduce); *d_film is owned by ctx. */
 int pbrtgpu_render_device(pbrtgpu_ctx *ctx, const pbrtgpu_render_params *params,
                           void **d_film, pbrtgpu_stats *stats_or_null);
+/* Copy the film left by pbrtgpu_render_device into a caller-owned device buffer (e.g. a tensor handed to NCCL). */
+int pbrtgpu_copy_film_device(pbrtgpu_ctx *ctx, void *d_dst, int64_t bytes);
+/* Profile mode: renders record a CUDA-event pair around every kernel launch and count
+ * traversal steps; pbrtgpu_get_profile returns the sums since profile mode was last set. */
+int pbrtgpu_set_profile(pbrtgpu_ctx *ctx, int on);
+int pbrtgpu_get_profile(pbrtgpu_ctx *ctx, pbrtgpu_profile *out);
 /* Run the render on this CUDA stream (cudaStream_t) instead of the ctx's own. */
 int pbrtgpu_set_stream(pbrtgpu_ctx *ctx, void *cuda_stream);
 

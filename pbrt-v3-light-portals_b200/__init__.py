@@ -78,7 +78,14 @@ class RenderParams(C.Structure):  # pbrtgpu_render_params
 
 class Stats(C.Structure):  # pbrtgpu_stats
     _fields_ = [("camera_rays", C.c_int64), ("closest_rays", C.c_int64), ("shadow_rays", C.c_int64),
-                ("scrubbed", C.c_int64), ("kernel_launches", C.c_int64), ("device_ms", C.c_float)]
+                ("scrubbed", C.c_int64), ("kernel_launches", C.c_int64), ("nee_closest_rays", C.c_int64), ("device_ms", C.c_float)]
+
+
+K_NAMES = ["raygen", "trace_closest", "shade", "trace_shadow", "trace_nee", "film"]
+
+
+class Profile(C.Structure):  # pbrtgpu_profile
+    _fields_ = [("ms", C.c_double * 6), ("launches", C.c_int64 * 6), ("node_tests", C.c_int64 * 6), ("prim_tests", C.c_int64 * 6)]
 
 
 _host = None
@@ -141,6 +148,10 @@ def gpu_lib():
         if hasattr(lib, "pbrtgpu_render"):
             lib.pbrtgpu_render.argtypes = [C.c_void_p, _p(RenderParams), C.c_void_p, _p(Stats)]
             lib.pbrtgpu_render_device.argtypes = [C.c_void_p, _p(RenderParams), _p(C.c_void_p), _p(Stats)]
+        if hasattr(lib, "pbrtgpu_set_profile"):
+            lib.pbrtgpu_set_profile.argtypes = [C.c_void_p, C.c_int]
+            lib.pbrtgpu_get_profile.argtypes = [C.c_void_p, _p(Profile)]
+            lib.pbrtgpu_copy_film_device.argtypes = [C.c_void_p, C.c_void_p, C.c_int64]
         if hasattr(lib, "pbrtgpu_halton_samples"):
             lib.pbrtgpu_halton_samples.argtypes = [C.c_void_p, _p(RenderParams), C.c_void_p, C.c_void_p, C.c_void_p,
                                                    C.c_int64, C.c_void_p]
@@ -260,6 +271,19 @@ class GpuContext:
         stats = Stats()
         self._check(self._lib.pbrtgpu_render(self._h, C.byref(params), film.ctypes.data, C.byref(stats)))
         return film, stats
+
+    def set_profile(self, on):
+        self._check(self._lib.pbrtgpu_set_profile(self._h, int(bool(on))))
+
+    def get_profile(self):
+        """{kernel: {ms, launches, node_tests, prim_tests}} summed since set_profile(True)."""
+        p = Profile()
+        self._check(self._lib.pbrtgpu_get_profile(self._h, C.byref(p)))
+        return {K_NAMES[k]: {"ms": p.ms[k], "launches": p.launches[k], "node_tests": p.node_tests[k], "prim_tests": p.prim_tests[k]}
+                for k in range(6)}
+
+    def copy_film_device(self, dst_ptr, nbytes):
+        self._check(self._lib.pbrtgpu_copy_film_device(self._h, C.c_void_p(dst_ptr), int(nbytes)))
 
     def render_device(self, params):
         d_film = C.c_void_p()

@@ -26,13 +26,15 @@ enum {  // BxDFType, reflection.h:119-127
     BSDF_ALL = 31
 };
 
-enum LobeKind { LOBE_LAMBERT, LOBE_OREN_NAYAR, LOBE_MICRO_REFL, LOBE_MICRO_TRANS, LOBE_FRESNEL_SPECULAR, LOBE_SPEC_REFL_NOOP };
+enum LobeKind { LOBE_LAMBERT, LOBE_OREN_NAYAR, LOBE_MICRO_REFL, LOBE_MICRO_TRANS, LOBE_FRESNEL_SPECULAR, LOBE_SPEC_REFL_NOOP,
+                LOBE_MICRO_REFL_COND /* MicrofacetReflection with FresnelConductor(1, T, K): metal */ };
 
 struct Lobe {
     int kind;
     int type;      // BxDFType bits
     Spec R;        // R (reflection lobes) or T (MICRO_TRANS); FRESNEL_SPECULAR keeps T in T
     Spec T;
+    Spec K;        // conductor absorption (metal)
     float a, b;    // OrenNayar A,B | alphax, alphay
     float etaA, etaB;  // dielectric Fresnel (etaI, etaT) / transmission indices
 };
@@ -90,6 +92,30 @@ PG_HD float frDielectric(float cosThetaI, float etaI, float etaT) {
     float Rparl = ((etaT * cosThetaI) - (etaI * cosThetaT)) / ((etaT * cosThetaI) + (etaI * cosThetaT));
     float Rperp = ((etaI * cosThetaI) - (etaT * cosThetaT)) / ((etaI * cosThetaI) + (etaT * cosThetaT));
     return (Rparl * Rparl + Rperp * Rperp) / 2;
+}
+
+PG_HD Spec specSqrt(Spec s) { return spec(sqrtf(s.r), sqrtf(s.g), sqrtf(s.b)); }
+PG_HD Spec operator+(Spec a, float b) { return spec(a.r + b, a.g + b, a.b + b); }
+PG_HD Spec operator-(Spec a, float b) { return spec(a.r - b, a.g - b, a.b - b); }
+// FrConductor, reflection.cpp:71-94
+PG_HD Spec frConductor(float cosThetaI, Spec etai, Spec etat, Spec k) {
+    cosThetaI = clampf(cosThetaI, -1, 1);
+    Spec eta = etat / etai;
+    Spec etak = k / etai;
+    float cosThetaI2 = cosThetaI * cosThetaI;
+    float sinThetaI2 = (float)(1. - (double)cosThetaI2);
+    Spec eta2 = eta * eta;
+    Spec etak2 = etak * etak;
+    Spec t0 = eta2 - etak2 - sinThetaI2;
+    Spec a2plusb2 = specSqrt(t0 * t0 + 4 * eta2 * etak2);
+    Spec t1 = a2plusb2 + cosThetaI2;
+    Spec a = specSqrt(0.5f * (a2plusb2 + t0));
+    Spec t2 = (float)2 * cosThetaI * a;
+    Spec Rs = (t1 - t2) / (t1 + t2);
+    Spec t3 = cosThetaI2 * a2plusb2 + sinThetaI2 * sinThetaI2;
+    Spec t4 = t2 * sinThetaI2;
+    Spec Rp = Rs * (t3 - t4) / (t3 + t4);
+    return 0.5f * (Rp + Rs);
 }
 
 // ---- TrowbridgeReitzDistribution (sampleVisibleArea = true, the default)

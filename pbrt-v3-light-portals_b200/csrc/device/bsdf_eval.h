@@ -12,7 +12,8 @@ PG_HD Spec microReflF(const Lobe &l, V3 wo, V3 wi) {  // MicrofacetReflection::f
     if (cosThetaI == 0 || cosThetaO == 0) return spec(0.f);
     if (wh.x == 0 && wh.y == 0 && wh.z == 0) return spec(0.f);
     wh = normalize(wh);
-    float F = frDielectric(dot(wi, faceforward(wh, v3(0, 0, 1))), l.etaA, l.etaB);
+    float cosI = dot(wi, faceforward(wh, v3(0, 0, 1)));
+    Spec F = l.kind == LOBE_MICRO_REFL_COND ? frConductor(fabsf(cosI), spec(1.f), l.T, l.K) : spec(frDielectric(cosI, l.etaA, l.etaB));
     return l.R * trD(l.a, l.b, wh) * trG(l.a, l.b, wo, wi) * F / (4 * cosThetaI * cosThetaO);
 }
 
@@ -66,7 +67,8 @@ PG_HD Spec lobeF(const Lobe &l, V3 wo, V3 wi) {
     switch (l.kind) {
     case LOBE_LAMBERT: return l.R * kInvPi;
     case LOBE_OREN_NAYAR: return orenNayarF(l, wo, wi);
-    case LOBE_MICRO_REFL: return microReflF(l, wo, wi);
+    case LOBE_MICRO_REFL:
+    case LOBE_MICRO_REFL_COND: return microReflF(l, wo, wi);
     case LOBE_MICRO_TRANS: return microTransF(l, wo, wi);
     default: return spec(0.f);  // specular lobes
     }
@@ -76,7 +78,8 @@ PG_HD float lobePdf(const Lobe &l, V3 wo, V3 wi) {
     switch (l.kind) {
     case LOBE_LAMBERT:
     case LOBE_OREN_NAYAR: return sameHemisphere(wo, wi) ? absCosTheta(wi) * kInvPi : 0;
-    case LOBE_MICRO_REFL: {
+    case LOBE_MICRO_REFL:
+    case LOBE_MICRO_REFL_COND: {
         if (!sameHemisphere(wo, wi)) return 0;
         V3 wh = normalize(wo + wi);
         return trPdf(l.a, l.b, wo, wh) / (4 * dot(wo, wh));
@@ -95,7 +98,8 @@ PG_HD Spec lobeSample(const Lobe &l, V3 wo, float u0, float u1, V3 *wi, float *p
         if (wo.z < 0) wi->z *= -1;
         *pdf = lobePdf(l, wo, *wi);
         return lobeF(l, wo, *wi);
-    case LOBE_MICRO_REFL: {
+    case LOBE_MICRO_REFL:
+    case LOBE_MICRO_REFL_COND: {
         if (wo.z == 0) return spec(0.f);
         V3 wh = trSampleWh(l.a, l.b, wo, u0, u1);
         if (dot(wo, wh) < 0) return spec(0.f);
@@ -300,6 +304,13 @@ PG_HD void makeBSDF(const SurfInt &it, int tag, const float *mp, float wvl0, BSD
                 l.etaA = 1.f, l.etaB = eta;
             }
         }
+    } else if (tag == PBRTGPU_MAT_METAL) {  // materials/metal.cpp:60-82
+        Lobe &l = b->lobes[b->nLobes++];
+        l.kind = LOBE_MICRO_REFL_COND;
+        l.type = BSDF_REFLECTION | BSDF_GLOSSY;
+        l.R = spec(1.f);
+        l.T = loadSpec(mp), l.K = loadSpec(mp + 3);
+        l.a = PG_LD(mp + 6), l.b = PG_LD(mp + 7);
     } else if (tag == PBRTGPU_MAT_MIRROR) {
         Spec R = loadSpec(mp);
         if (!isBlack(R)) {

@@ -38,6 +38,10 @@ struct pbrtgpu_ctx {
     float lightFuncInt[2] = {0, 0};
     pg::DeviceBuffer filterTable;
     unsigned long long *dTotals = nullptr;          // cameraRays, closestRays, shadowRays, scrubbed
+    bool profile = false;                           // pbrtgpu_set_profile: event pairs per launch + traversal counters
+    double profMs[PBRTGPU_K_COUNT] = {0};
+    long long profLaunches[PBRTGPU_K_COUNT] = {0};
+    unsigned long long *dTraversalCounts = nullptr;
     bool hasNullMaterial = false;                   // some primitive has no material (path.cpp:108-113)
     // render scratch, grown on demand
     pg::DeviceBuffer scratch[16];

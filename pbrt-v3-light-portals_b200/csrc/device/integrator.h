@@ -62,6 +62,7 @@ struct WaveParams {
     F4 *neeHits;
     unsigned char *shadowOcc;
     WaveCounters *cnt;
+    unsigned long long *countTraversal;  // profile mode: {closest, shadow, nee} x {node tests, prim tests}; else null
 };
 
 #if defined(__CUDA_ARCH__)

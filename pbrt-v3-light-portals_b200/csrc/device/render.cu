@@ -34,16 +34,28 @@ __global__ void __launch_bounds__(kStageBlock) k_raygen(WaveParams w) {
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < w.nSlots; i += stride) stageRaygen(w, i);
 }
 
+// COUNT = profile mode: also accumulate node / primitive tests into w.countTraversal[2*which..]
+template <bool COUNT>
+__device__ __forceinline__ void flushCounts(const WaveParams &w, int which, const TraverseCounters &c) {
+    if (COUNT) {
+        atomicAdd(w.countTraversal + 2 * which, (unsigned long long)c.nodes);
+        atomicAdd(w.countTraversal + 2 * which + 1, (unsigned long long)c.prims);
+    }
+}
+
+template <bool COUNT>
 __global__ void __launch_bounds__(kTraceBlock) k_trace_closest(WaveParams w, int depth, int cur) {
     int n = w.cnt->nActive[depth];
     int stride = gridDim.x * blockDim.x;
     const F4 *rays = w.rays[cur];
+    TraverseCounters c = {0, 0};
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
         Ray ray = loadRay(rays, i);
         Hit h;
-        traverse<false>(w.sc.bvh, ray, &h);
+        traverse<false, COUNT>(w.sc.bvh, ray, &h, &c);
         w.hits[i] = f4(__int_as_float(h.prim), h.b0, h.b1, h.b2);
     }
+    flushCounts<COUNT>(w, 0, c);
 }
 
 __global__ void __launch_bounds__(kStageBlock) k_shade(WaveParams w, int depth, int cur) {
@@ -52,26 +64,32 @@ __global__ void __launch_bounds__(kStageBlock) k_shade(WaveParams w, int depth, 
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) stageShade(w, depth, cur, i);
 }
 
+template <bool COUNT>
 __global__ void __launch_bounds__(kTraceBlock) k_trace_shadow(WaveParams w, int depth) {
     int n = w.cnt->nShadow[depth];
     int stride = gridDim.x * blockDim.x;
+    TraverseCounters c = {0, 0};
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
         Ray ray = loadRay(w.shadowRays, i);
-        bool occ = traverse<true>(w.sc.bvh, ray, nullptr);
+        bool occ = traverse<true, COUNT>(w.sc.bvh, ray, nullptr, &c);
         stageShadowResolve(w, i, occ);
     }
+    flushCounts<COUNT>(w, 1, c);
 }
 
+template <bool COUNT>
 __global__ void __launch_bounds__(kTraceBlock) k_trace_nee(WaveParams w, int depth) {
     int n = w.cnt->nNee[depth];
     int stride = gridDim.x * blockDim.x;
+    TraverseCounters c = {0, 0};
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
         Ray ray = loadRay(w.neeRays, i);
         Hit h;
-        traverse<false>(w.sc.bvh, ray, &h);
+        traverse<false, COUNT>(w.sc.bvh, ray, &h, &c);
         w.neeHits[i] = f4(__int_as_float(h.prim), h.b0, h.b1, h.b2);
         stageNeeResolve(w, i);
     }
+    flushCounts<COUNT>(w, 2, c);
 }
 
 __global__ void __launch_bounds__(kStageBlock) k_film(WaveParams w) {
@@ -82,11 +100,12 @@ __global__ void __launch_bounds__(kStageBlock) k_film(WaveParams w) {
 // fold one batch's counters into the running totals, then clear them for the next batch
 __global__ void k_batch_stats(WaveCounters *cnt, unsigned long long *totals, int depths) {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
-    unsigned long long closest = 0, shadow = 0;
+    unsigned long long closest = 0, shadow = 0, nee = 0;
     for (int d = 0; d <= depths; ++d) closest += (unsigned long long)cnt->nActive[d];
-    for (int d = 0; d < depths; ++d) closest += (unsigned long long)cnt->nNee[d], shadow += (unsigned long long)cnt->nShadow[d];
+    for (int d = 0; d < depths; ++d) nee += (unsigned long long)cnt->nNee[d], shadow += (unsigned long long)cnt->nShadow[d];
     totals[0] += (unsigned long long)cnt->nActive[0];
-    totals[1] += closest;
+    totals[1] += closest + nee;
+    totals[4] += nee;
     totals[2] += shadow;
     totals[3] += cnt->scrubbed;
     for (int d = 0; d <= kMaxDepthSlots; ++d) cnt->nActive[d] = 0;

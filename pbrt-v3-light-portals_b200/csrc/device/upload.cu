@@ -71,7 +71,7 @@ int pbrtgpu_create(int cuda_device, pbrtgpu_ctx **out) {
         for (size_t i = 0; i < primes.size(); ++i) sums[i] = acc, acc += primes[i];
         if ((e = cudaMalloc((void **)&ctx->dPrimes, primes.size() * sizeof(int))) != cudaSuccess) return bail(e, "cudaMalloc(primes)");
         if ((e = cudaMalloc((void **)&ctx->dPrimeSums, primes.size() * sizeof(int))) != cudaSuccess) return bail(e, "cudaMalloc(primeSums)");
-        if ((e = cudaMalloc((void **)&ctx->dTotals, 4 * sizeof(unsigned long long))) != cudaSuccess) return bail(e, "cudaMalloc(totals)");
+        if ((e = cudaMalloc((void **)&ctx->dTotals, 5 * sizeof(unsigned long long))) != cudaSuccess) return bail(e, "cudaMalloc(totals)");
         cudaMemcpy(ctx->dPrimes, primes.data(), primes.size() * sizeof(int), cudaMemcpyHostToDevice);
         cudaMemcpy(ctx->dPrimeSums, sums.data(), primes.size() * sizeof(int), cudaMemcpyHostToDevice);
     }
@@ -90,6 +90,7 @@ void pbrtgpu_destroy(pbrtgpu_ctx *ctx) {
     if (ctx->dPrimes) cudaFree(ctx->dPrimes);
     if (ctx->dPrimeSums) cudaFree(ctx->dPrimeSums);
     if (ctx->dTotals) cudaFree(ctx->dTotals);
+    if (ctx->dTraversalCounts) cudaFree(ctx->dTraversalCounts);
     for (auto &b : ctx->wave)
         if (b.p) cudaFree(b.p);
     if (ctx->lightDist.p) cudaFree(ctx->lightDist.p);

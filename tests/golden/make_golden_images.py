@@ -1,0 +1,54 @@
+"""Generates tests/golden/images.npz: the reference binary's own renders
+(oracle/_ref/pbrt, built from /root/reference by oracle/Makefile; one thread,
+float PFM output) of the small scenes in tests/scenes.  Run in the development
+container, where /root/reference exists:
+    make -C oracle ref && python tests/golden/make_golden_images.py
+The tier-2 parity tests compare the CUDA path with these images.
+"""
+import os
+import subprocess
+import sys
+import tempfile
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.join(ROOT, "tools"))
+from dev_compare import read_pfm  # noqa: E402
+
+# name -> (scene file, text substitutions)
+CASES = {
+    "box_glass": ("box_glass.pbrt", {}),
+    "sphere_lights": ("sphere_lights.pbrt", {}),
+    "portal_room_light": ("portal_room.pbrt", {"STRATEGY": "light"}),
+    "portal_room_portal": ("portal_room.pbrt", {"STRATEGY": "portal"}),
+    "portal_room_projection": ("portal_room.pbrt", {"STRATEGY": "projection"}),
+    "tri_soup": ("tri_soup.pbrt", {}),
+}
+
+
+def scene_text(case):
+    fn, subs = CASES[case]
+    text = open(os.path.join(ROOT, "tests", "scenes", fn)).read()
+    for k, v in subs.items():
+        text = text.replace(k, v)
+    return text
+
+
+def main():
+    pbrt = os.path.join(ROOT, "oracle", "_ref", "pbrt")
+    out = {}
+    for case in CASES:
+        with tempfile.TemporaryDirectory() as d:
+            sp = os.path.join(d, "s.pbrt")
+            open(sp, "w").write(scene_text(case))
+            img = os.path.join(d, "o.pfm")
+            subprocess.check_call([pbrt, "--nthreads", "1", "--quiet", "--minloglevel", "2", "--outfile", img, sp],
+                                  stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+            out[case] = read_pfm(img)
+            print(case, out[case].shape, float(out[case].mean()))
+    np.savez_compressed(os.path.join(ROOT, "tests", "golden", "images.npz"), **out)
+
+
+if __name__ == "__main__":
+    main()

@@ -130,3 +130,28 @@ def hostsim_any(lib, view, rays, threads=8):
 
 def bits(a):
     return np.ascontiguousarray(a, np.float32).view(np.uint32)
+
+
+# ---------------------------------------------------------------- images (tier 2)
+
+def image_stats(ours, ref):
+    """rel_rmse = RMSE / mean(ref); bad_frac = share of pixels whose worst channel is off by
+    more than 1 % (relative to max(|ref|, 0.1 % of the image mean))."""
+    d = ours.astype(np.float64) - ref.astype(np.float64)
+    mean = max(float(ref.astype(np.float64).mean()), 1e-12)
+    rel = np.abs(d) / np.maximum(np.abs(ref), 1e-3 * mean)
+    return {"rel_rmse": float(np.sqrt((d ** 2).mean()) / mean), "bad_frac": float((rel.max(axis=2) > 0.01).mean()),
+            "mean_rel": float(abs(ours.astype(np.float64).mean() - mean) / mean)}
+
+
+def hostsim_render(lib, scene, params=None, threads=8):
+    """The device stage functions stepped on the CPU (tests/hostsim): returns (rgb, stats4)."""
+    lib.hostsim_render.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+    params = params if params is not None else scene.params
+    h = C.c_void_p(lib.hostsim_create(C.byref(scene.view)))
+    cb = params.cropped_bounds
+    film = np.zeros((cb[3] - cb[1], cb[2] - cb[0], 4), np.float32)
+    st = (C.c_int64 * 4)()
+    lib.hostsim_render(h, C.byref(params), film.ctypes.data, st, threads)
+    lib.hostsim_destroy(h)
+    return scene.film_to_rgb(film), film, list(st)

@@ -4,6 +4,12 @@
 
 namespace pg {
 
+#if !defined(__CUDACC__) && defined(PG_HOST_TRACE)
+#define PG_TRACE(...) fprintf(stderr, __VA_ARGS__)
+#else
+#define PG_TRACE(...)
+#endif
+
 // ---- stage 3: one path vertex (the body of path.cpp:81-187 after scene.Intersect).
 // pos = position in the depth-d closest-hit queue; cur = which of the two
 // ping-pong queues holds depth d.
@@ -21,6 +27,7 @@ PG_HD void stageShade(const WaveParams &w, int depth, int cur, int pos) {
     bool found = prim >= 0;
     SurfInt it;
     if (found) it = hitInteraction(w.sc, prim, hit.y, hit.z, hit.w, ray);
+    PG_TRACE("shade d=%d slot=%d prim=%d o=(%.9g %.9g %.9g) d=(%.9g %.9g %.9g) p=(%.9g %.9g %.9g) n=(%g %g %g) bounces=%d\n", depth, slot, prim, ray.o.x, ray.o.y, ray.o.z, ray.d.x, ray.d.y, ray.d.z, it.p.x, it.p.y, it.p.z, it.n.x, it.n.y, it.n.z, bounces);
 
     // emitted light at the vertex or from the environment (path.cpp:91-101)
     if (bounces == 0 || specularBounce) {
@@ -52,6 +59,7 @@ PG_HD void stageShade(const WaveParams &w, int depth, int cur, int pos) {
                     storeRay(w.shadowRays, sp, nee.shadowRay);
                     w.shadowContrib[sp] = f4(nee.shadowContrib.r, nee.shadowContrib.g, nee.shadowContrib.b, bitsToFloat((unsigned)slot));
                 }
+                PG_TRACE("  nee shadow=%d closest=%d mode=%d contrib=(%g %g %g) ray o=(%.9g %.9g %.9g) d=(%.9g %.9g %.9g)\n", (int)nee.hasShadow, (int)nee.hasClosest, nee.mode, nee.closestContrib.r, nee.closestContrib.g, nee.closestContrib.b, nee.closestRay.o.x, nee.closestRay.o.y, nee.closestRay.o.z, nee.closestRay.d.x, nee.closestRay.d.y, nee.closestRay.d.z);
                 if (nee.hasClosest) {
                     int np = atomicIncInt(&w.cnt->nNee[depth]);
                     storeRay(w.neeRays, np, nee.closestRay);
@@ -127,6 +135,7 @@ PG_HD void stageNeeResolve(const WaveParams &w, int pos) {
             Li = infiniteLe(w.sc.lightParams + PBRTGPU_LIGHT_STRIDE * (size_t)light, ray.d);
     } else if (mode == NEE_ANY_OR_LIGHT)
         Li = loadSpec(w.sc.lightParams + PBRTGPU_LIGHT_STRIDE * (size_t)light);
+    PG_TRACE("  nee resolve slot=%d prim=%d Li=(%g %g %g) b=(%g %g %g)\n", slot, prim, Li.r, Li.g, Li.b, hit.y, hit.z, hit.w);
     if (isBlack(Li)) return;
     F4 Lq = w.L[slot];
     Lq.x += c.x * Li.r, Lq.y += c.y * Li.g, Lq.z += c.z * Li.b;

@@ -30,6 +30,13 @@ inline std::vector<int> firstPrimes(int n = kPrimeTableSize) {
     return primes;
 }
 
+// floor(2^64 / p) + 1 for each prime (see sampler.h: exact a / p for a < 2^32)
+inline std::vector<unsigned long long> primeMagics(const std::vector<int> &primes) {
+    std::vector<unsigned long long> m;
+    for (int p : primes) m.push_back(~0ull / (unsigned long long)p + 1);
+    return m;
+}
+
 struct Pcg32 {  // rng.h:56-148
     uint64_t state = 0x853c49e6748fea9bULL, inc = 0xda3e39cb94b95bdbULL;
     uint32_t uniformUInt32() {

@@ -17,7 +17,7 @@
 
 #if defined(__CUDACC__)
 #define PG_HD __host__ __device__ __forceinline__
-#define PG_HD_NOINLINE __host__ __device__
+#define PG_HD_NOINLINE __host__ __device__ __noinline__ inline
 #else
 #define PG_HD inline
 #define PG_HD_NOINLINE inline

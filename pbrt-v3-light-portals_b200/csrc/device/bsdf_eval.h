@@ -63,7 +63,7 @@ PG_HD Spec orenNayarF(const Lobe &l, V3 wo, V3 wi) {
     return l.R * kInvPi * (l.a + l.b * maxCos * sinAlpha * tanBeta);
 }
 
-PG_HD Spec lobeF(const Lobe &l, V3 wo, V3 wi) {
+PG_HD_NOINLINE Spec lobeF(const Lobe &l, V3 wo, V3 wi) {
     switch (l.kind) {
     case LOBE_LAMBERT: return l.R * kInvPi;
     case LOBE_OREN_NAYAR: return orenNayarF(l, wo, wi);
@@ -74,7 +74,7 @@ PG_HD Spec lobeF(const Lobe &l, V3 wo, V3 wi) {
     }
 }
 
-PG_HD float lobePdf(const Lobe &l, V3 wo, V3 wi) {
+PG_HD_NOINLINE float lobePdf(const Lobe &l, V3 wo, V3 wi) {
     switch (l.kind) {
     case LOBE_LAMBERT:
     case LOBE_OREN_NAYAR: return sameHemisphere(wo, wi) ? absCosTheta(wi) * kInvPi : 0;
@@ -90,7 +90,7 @@ PG_HD float lobePdf(const Lobe &l, V3 wo, V3 wi) {
 }
 
 // BxDF::Sample_f of each lobe; *pdf must be 0 on entry (BSDF::Sample_f sets it).
-PG_HD Spec lobeSample(const Lobe &l, V3 wo, float u0, float u1, V3 *wi, float *pdf, int *sampledType) {
+PG_HD_NOINLINE Spec lobeSample(const Lobe &l, V3 wo, float u0, float u1, V3 *wi, float *pdf, int *sampledType) {
     switch (l.kind) {
     case LOBE_LAMBERT:
     case LOBE_OREN_NAYAR:
@@ -155,7 +155,7 @@ PG_HD int bsdfNumComponents(const BSDF &b, int flags) {
     return n;
 }
 
-PG_HD Spec bsdfF(const BSDF &b, V3 woW, V3 wiW, int flags) {
+PG_HD_NOINLINE Spec bsdfF(const BSDF &b, V3 woW, V3 wiW, int flags) {
     V3 wi = bsdfWorldToLocal(b, wiW), wo = bsdfWorldToLocal(b, woW);
     if (wo.z == 0) return spec(0.f);
     bool reflect = dot(wiW, b.ng) * dot(woW, b.ng) > 0;
@@ -167,7 +167,7 @@ PG_HD Spec bsdfF(const BSDF &b, V3 woW, V3 wiW, int flags) {
     return f;
 }
 
-PG_HD float bsdfPdf(const BSDF &b, V3 woW, V3 wiW, int flags) {
+PG_HD_NOINLINE float bsdfPdf(const BSDF &b, V3 woW, V3 wiW, int flags) {
     if (b.nLobes == 0) return 0.f;
     V3 wo = bsdfWorldToLocal(b, woW), wi = bsdfWorldToLocal(b, wiW);
     if (wo.z == 0) return 0.f;
@@ -181,7 +181,7 @@ PG_HD float bsdfPdf(const BSDF &b, V3 woW, V3 wiW, int flags) {
     return matchingComps > 0 ? pdf / matchingComps : 0.f;
 }
 
-PG_HD Spec bsdfSampleF(const BSDF &b, V3 woW, V3 *wiW, float u0, float u1, float *pdf, int type, int *sampledType) {
+PG_HD_NOINLINE Spec bsdfSampleF(const BSDF &b, V3 woW, V3 *wiW, float u0, float u1, float *pdf, int type, int *sampledType) {
     int matchingComps = bsdfNumComponents(b, type);
     if (matchingComps == 0) {
         *pdf = 0;
@@ -232,7 +232,7 @@ PG_HD Spec bsdfSampleF(const BSDF &b, V3 woW, V3 *wiW, float u0, float u1, float
 // Material::ComputeScatteringFunctions for the material table of pbrtgpu.h
 // (allowMultipleLobes = true, TransportMode::Radiance, as path.cpp:107 calls it).
 // wvl0 = hero wavelength in nm, used by dispersive_glass only.
-PG_HD void makeBSDF(const SurfInt &it, int tag, const float *mp, float wvl0, BSDF *b) {
+PG_HD_NOINLINE void makeBSDF(const SurfInt &it, int tag, const float *mp, float wvl0, BSDF *b) {
     b->ns = it.ns;
     b->ng = it.n;
     b->ss = normalize(it.dpdus);

@@ -31,6 +31,7 @@ struct pbrtgpu_ctx {
     std::vector<void *> sceneAllocs;  // freed on re-upload / destroy
     // Halton tables (uploaded at create)
     unsigned short *dPerms = nullptr;
+    unsigned long long *dPrimeMagic = nullptr;
     int *dPrimes = nullptr, *dPrimeSums = nullptr;  // first 1000 primes and their running sums
     // wavefront state of the path integrator (render.cu), grown on demand
     pg::DeviceBuffer wave[24];
@@ -42,6 +43,7 @@ struct pbrtgpu_ctx {
     double profMs[PBRTGPU_K_COUNT] = {0};
     long long profLaunches[PBRTGPU_K_COUNT] = {0};
     unsigned long long *dTraversalCounts = nullptr;
+    bool hasInfiniteLight = false;
     bool hasNullMaterial = false;                   // some primitive has no material (path.cpp:108-113)
     // render scratch, grown on demand
     pg::DeviceBuffer scratch[16];

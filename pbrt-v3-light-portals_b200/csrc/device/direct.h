@@ -52,7 +52,7 @@ PG_HD Spec areaLightL(const DevScene &sc, int li, V3 n, V3 w) {
 }
 
 // Light::Sample_Li.  Returns Li; fills wi, pdf and the point the visibility ray aims at.
-PG_HD Spec lightSampleLi(const DevScene &sc, int li, const SurfInt &it, float u0, float u1, V3 *wi, float *pdf, ShapeSample *pL) {
+PG_HD_NOINLINE Spec lightSampleLi(const DevScene &sc, int li, const SurfInt &it, float u0, float u1, V3 *wi, float *pdf, ShapeSample *pL) {
     int tag = PG_LD(sc.lightTag + li);
     const float *lp = sc.lightParams + PBRTGPU_LIGHT_STRIDE * (size_t)li;
     pL->pError = v3(0, 0, 0);
@@ -89,7 +89,7 @@ PG_HD Spec lightSampleLi(const DevScene &sc, int li, const SurfInt &it, float u0
     return loadSpec(lp);
 }
 
-PG_HD float lightPdfLi(const DevScene &sc, int li, const SurfInt &it, V3 wi) {
+PG_HD_NOINLINE float lightPdfLi(const DevScene &sc, int li, const SurfInt &it, V3 wi) {
     int tag = PG_LD(sc.lightTag + li);
     if (tag == PBRTGPU_LIGHT_DIFFUSE_AREA || tag == PBRTGPU_LIGHT_PORTAL_AREA)
         return shapePdfRef(sc.bvh, PG_LD(sc.lightPrim + li), it.p, it.pError, it.n, wi);
@@ -104,7 +104,7 @@ PG_HD float powerHeuristic(float fPdf, float gPdf) {  // PowerHeuristic(1, f, 1,
 
 // The portal branch of EstimateDirect.  u1 is what the reference passes as u1:
 // the SCATTERING sample (Q5); u2 is unused there as well.
-PG_HD void estimateDirectPortal(const DevScene &sc, int li, const SurfInt &it, const BSDF &bsdf, float u1x, float u1y,
+PG_HD_NOINLINE void estimateDirectPortal(const DevScene &sc, int li, const SurfInt &it, const BSDF &bsdf, float u1x, float u1y,
                                 Spec scale, NeeRequest *out) {
     const int flagsNS = BSDF_ALL & ~BSDF_SPECULAR;
     int strat = PG_LD(sc.lightStrategy + li);

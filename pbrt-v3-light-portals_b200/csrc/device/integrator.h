@@ -19,6 +19,8 @@ struct WaveCounters {
     int nActive[kMaxDepthSlots + 1];  // closest-hit queue length entering depth d
     int nShadow[kMaxDepthSlots];      // any-hit NEE rays generated at depth d
     int nNee[kMaxDepthSlots];         // closest-hit NEE rays generated at depth d
+    int nHit[kMaxDepthSlots];         // of the nActive[d] rays: how many hit something (queue hitIdx) ...
+    int nMiss[kMaxDepthSlots];        // ... and how many escaped (queue missIdx)
     unsigned long long cameraRays, closestRays, shadowRays, scrubbed;
 };
 
@@ -54,6 +56,7 @@ struct WaveParams {
     F4 *rays[2];           // closest-hit rays of the current / next depth, 2 x float4 each
     int *qSlot[2];
     F4 *hits;              // {prim slot (int), b0, b1, b2}
+    int *hitIdx, *missIdx; // positions of the current queue that hit / escaped, compacted by the trace kernel
     F4 *shadowRays;        // 2 x float4 each
     F4 *shadowContrib;     // rgb, slot (int)
     F4 *neeRays;
@@ -150,7 +153,7 @@ PG_HD void stageRaygen(const WaveParams &w, int slot) {
 }
 
 // Interaction::n and emission of a hit, for SurfaceInteraction::Le(w)
-PG_HD SurfInt hitInteraction(const DevScene &sc, int prim, float b0, float b1, float b2, const Ray &ray) {
+PG_HD_NOINLINE SurfInt hitInteraction(const DevScene &sc, int prim, float b0, float b1, float b2, const Ray &ray) {
     const F4 *tp = sc.bvh.tris + 3 * (size_t)prim;
     int tag = f2i(PG_LDG(tp).w);
     int type = tag & kTagTypeMask;

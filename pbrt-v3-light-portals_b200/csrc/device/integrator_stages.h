@@ -10,7 +10,24 @@ namespace pg {
 #define PG_TRACE(...)
 #endif
 
-// ---- stage 3: one path vertex (the body of path.cpp:81-187 after scene.Intersect).
+// ---- stage 2b: a path ray that escaped.  Environment light on the camera ray
+// or after a specular bounce (path.cpp:91-101), then the path ends (path.cpp:104).
+PG_HD void stageMiss(const WaveParams &w, int cur, int pos) {
+    int slot = w.qSlot[cur][pos];
+    int flags = w.flags[slot];
+    int bounces = flags & 255;
+    bool specularBounce = (flags >> 8) & 1;
+    if (!(bounces == 0 || specularBounce)) return;
+    Ray ray = loadRay(w.rays[cur], pos);
+    F4 Lq = w.L[slot], bq = w.beta[slot];
+    Spec L = spec(Lq.x, Lq.y, Lq.z), beta = spec(bq.x, bq.y, bq.z);
+    for (int i = 0; i < w.sc.nLights; ++i)
+        if (PG_LD(w.sc.lightTag + i) == PBRTGPU_LIGHT_INFINITE)
+            L += beta * infiniteLe(w.sc.lightParams + PBRTGPU_LIGHT_STRIDE * (size_t)i, ray.d);
+    w.L[slot] = f4(L.r, L.g, L.b, Lq.w);
+}
+
+// ---- stage 3: one path vertex (the body of path.cpp:81-187 after scene.Intersect found a hit).
 // pos = position in the depth-d closest-hit queue; cur = which of the two
 // ping-pong queues holds depth d.
 PG_HD void stageShade(const WaveParams &w, int depth, int cur, int pos) {
@@ -24,19 +41,12 @@ PG_HD void stageShade(const WaveParams &w, int depth, int cur, int pos) {
     int flags = w.flags[slot];
     int bounces = flags & 255;
     bool specularBounce = (flags >> 8) & 1;
-    bool found = prim >= 0;
-    SurfInt it;
-    if (found) it = hitInteraction(w.sc, prim, hit.y, hit.z, hit.w, ray);
+    const bool found = true;
+    SurfInt it = hitInteraction(w.sc, prim, hit.y, hit.z, hit.w, ray);
     PG_TRACE("shade d=%d slot=%d prim=%d o=(%.9g %.9g %.9g) d=(%.9g %.9g %.9g) p=(%.9g %.9g %.9g) n=(%g %g %g) bounces=%d\n", depth, slot, prim, ray.o.x, ray.o.y, ray.o.z, ray.d.x, ray.d.y, ray.d.z, it.p.x, it.p.y, it.p.z, it.n.x, it.n.y, it.n.z, bounces);
 
-    // emitted light at the vertex or from the environment (path.cpp:91-101)
-    if (bounces == 0 || specularBounce) {
-        if (found) L += beta * hitLe(w.sc, prim, it.n, -ray.d);
-        else
-            for (int i = 0; i < w.sc.nLights; ++i)
-                if (PG_LD(w.sc.lightTag + i) == PBRTGPU_LIGHT_INFINITE)
-                    L += beta * infiniteLe(w.sc.lightParams + PBRTGPU_LIGHT_STRIDE * (size_t)i, ray.d);
-    }
+    // emitted light at the vertex (path.cpp:91-96)
+    if (bounces == 0 || specularBounce) L += beta * hitLe(w.sc, prim, it.n, -ray.d);
     bool alive = found && bounces < w.maxDepth;
     Ray next;
     if (alive) {

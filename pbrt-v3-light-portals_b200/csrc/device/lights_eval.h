@@ -11,7 +11,7 @@ namespace pg {
 enum { kInfRow = 40, kInfMargCdf = 4, kInfMargInt = 5 };
 
 // Shape::Pdf(ref, wi) for one primitive slot (Sphere::Pdf overrides it outside the sphere).
-PG_HD float shapePdfRef(const DevBVH &bvh, int slot, V3 refP, V3 refPError, V3 refN, V3 wi) {
+PG_HD_NOINLINE float shapePdfRef(const DevBVH &bvh, int slot, V3 refP, V3 refPError, V3 refN, V3 wi) {
     const F4 *tp = bvh.tris + 3 * (size_t)slot;
     F4 a = PG_LDG(tp);
     int tag = f2i(a.w);
@@ -84,7 +84,7 @@ PG_HD float sampleContinuous2(float f0, float f1, float c1, float funcInt, float
     *pdf = (funcInt > 0) ? (offset ? f1 : f0) / funcInt : 0;
     return (offset + du) / 2;
 }
-PG_HD Spec infiniteSampleLi(const float *lp, float u0, float u1, V3 *wi, float *pdf, float *uvOut) {
+PG_HD_NOINLINE Spec infiniteSampleLi(const float *lp, float u0, float u1, V3 *wi, float *pdf, float *uvOut) {
     float pdfs[2];
     int v, dummy;
     // Distribution2D::SampleContinuous: marginal over rows (its func = the rows' funcInt), then the row

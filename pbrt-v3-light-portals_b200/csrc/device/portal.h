@@ -35,7 +35,7 @@ PG_HD bool portalInFront(const PortalRec &po, const M44 &lightW2O, V3 p) {
 
 // Portal choice.  Returns: -2 = behind every portal (fall back to light
 // sampling), -1 = contributes nothing, else the selected portal and its pdf.
-PG_HD int portalSelect(const float *portals, int nPortals, const M44 &lightW2O, V3 p, float u, float *portalPdf) {
+PG_HD_NOINLINE int portalSelect(const float *portals, int nPortals, const M44 &lightW2O, V3 p, float u, float *portalPdf) {
     bool behindAll = true;
     float sum = 0;
     for (int i = 0; i < nPortals; ++i)
@@ -79,7 +79,7 @@ PG_HD void portalSampleUniform(const PortalRec &po, const M44 &lightO2W, V3 refP
 }
 
 // AAPortal::SampleProj
-PG_HD void portalSampleProj(const PortalRec &po, const PlaneParams &light, const M44 &lightW2O, V3 refP, float u0, V3 *wi,
+PG_HD_NOINLINE void portalSampleProj(const PortalRec &po, const PlaneParams &light, const M44 &lightW2O, V3 refP, float u0, V3 *wi,
                             float *pdf) {
     V3 dLo = normalize(refP - light.lo);
     V3 dHi = normalize(refP - light.hi);

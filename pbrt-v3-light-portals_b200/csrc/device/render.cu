@@ -53,15 +53,26 @@ __global__ void __launch_bounds__(kTraceBlock) k_trace_closest(WaveParams w, int
         Ray ray = loadRay(rays, i);
         Hit h;
         traverse<false, COUNT>(w.sc.bvh, ray, &h, &c);
-        w.hits[i] = f4(__int_as_float(h.prim), h.b0, h.b1, h.b2);
+        if (h.prim >= 0) {
+            w.hits[i] = f4(__int_as_float(h.prim), h.b0, h.b1, h.b2);
+            w.hitIdx[atomicIncInt(&w.cnt->nHit[depth])] = i;
+        } else
+            w.missIdx[atomicIncInt(&w.cnt->nMiss[depth])] = i;
     }
     flushCounts<COUNT>(w, 0, c);
 }
 
 __global__ void __launch_bounds__(kStageBlock) k_shade(WaveParams w, int depth, int cur) {
-    int n = w.cnt->nActive[depth];
+    int n = w.cnt->nHit[depth];
     int stride = gridDim.x * blockDim.x;
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) stageShade(w, depth, cur, i);
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) stageShade(w, depth, cur, w.hitIdx[i]);
+}
+
+// escaped rays: only launched when the scene has an infinite light
+__global__ void __launch_bounds__(kStageBlock) k_miss(WaveParams w, int depth, int cur) {
+    int n = w.cnt->nMiss[depth];
+    int stride = gridDim.x * blockDim.x;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) stageMiss(w, cur, w.missIdx[i]);
 }
 
 template <bool COUNT>
@@ -109,7 +120,7 @@ __global__ void k_batch_stats(WaveCounters *cnt, unsigned long long *totals, int
     totals[2] += shadow;
     totals[3] += cnt->scrubbed;
     for (int d = 0; d <= kMaxDepthSlots; ++d) cnt->nActive[d] = 0;
-    for (int d = 0; d < kMaxDepthSlots; ++d) cnt->nShadow[d] = cnt->nNee[d] = 0;
+    for (int d = 0; d < kMaxDepthSlots; ++d) cnt->nShadow[d] = cnt->nNee[d] = cnt->nHit[d] = cnt->nMiss[d] = 0;
     cnt->scrubbed = 0;
 }
 
@@ -145,7 +156,7 @@ extern "C" int pbrtgpu_halton_samples(pbrtgpu_ctx *ctx, const pbrtgpu_render_par
         if (dim[i] < 0 || dim[i] >= kPrimeTableSize) return ctx->fail(PBRTGPU_ERR_INVALID, "HaltonSampler can only sample %d dimensions.", kPrimeTableSize);
     PG_CUDA(ctx, cudaSetDevice(ctx->device));
     HaltonParams h = makeHaltonParams(params->sample_bounds, params->sample_at_pixel_center);
-    h.primes = ctx->dPrimes, h.primeSums = ctx->dPrimeSums, h.perms = ctx->dPerms;
+    h.primes = ctx->dPrimes, h.primeSums = ctx->dPrimeSums, h.perms = ctx->dPerms, h.primeMagic = ctx->dPrimeMagic;
     int rc;
     size_t bytes = (size_t)n * (8 + 8 + 4 + 4);
     if ((rc = ensureBuffer(ctx, ctx->scratch[2], bytes)) != PBRTGPU_OK) return rc;

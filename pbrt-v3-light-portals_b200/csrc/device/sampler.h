@@ -25,6 +25,7 @@ struct HaltonParams {
     int sampleAtPixelCenter;
     const int *primes;             // 1000 entries
     const int *primeSums;          // 1000 entries
+    const unsigned long long *primeMagic;  // 1000 entries: floor(2^64 / p) + 1, so that a / p = mulhi64(a, magic) for a < 2^32
     const unsigned short *perms;   // 3,682,913 entries
 };
 
@@ -88,8 +89,20 @@ PG_HD float radicalInverseBase(unsigned base, unsigned long long a) {
     return minf((float)reversedDigits * invBaseN, kOneMinusEpsilon);
 }
 
-// ScrambledRadicalInverseSpecialized<base>, lowdiscrepancy.cpp:406-423
-PG_HD float scrambledRadicalInverseBase(unsigned base, const unsigned short *perm, unsigned long long a) {
+PG_HD unsigned long long mulhi64(unsigned long long a, unsigned long long b) {
+#if defined(__CUDA_ARCH__)
+    return __umul64hi(a, b);
+#else
+    return (unsigned long long)(((unsigned __int128)a * (unsigned __int128)b) >> 64);
+#endif
+}
+
+// ScrambledRadicalInverseSpecialized<base>, lowdiscrepancy.cpp:406-423.  The
+// quotient a / base is taken as mulhi64(a, magic) once a fits 32 bits: with
+// magic = floor(2^64 / base) + 1 the product overshoots a / base by less than
+// 2^-32, which cannot carry past the fraction's distance (>= 1 / base) to the
+// next integer -- so the digits are the reference's.
+PG_HD float scrambledRadicalInverseBase(unsigned base, unsigned long long magic, const unsigned short *perm, unsigned long long a) {
     const float invBase = (float)1 / (float)base;
     unsigned long long reversedDigits = 0;
     float invBaseN = 1;
@@ -102,7 +115,7 @@ PG_HD float scrambledRadicalInverseBase(unsigned base, const unsigned short *per
     }
     unsigned a32 = (unsigned)a;
     while (a32) {
-        unsigned next = a32 / base;
+        unsigned next = (unsigned)mulhi64((unsigned long long)a32, magic);
         unsigned digit = a32 - next * base;
         reversedDigits = reversedDigits * base + PG_LD(perm + digit);
         invBaseN *= invBase;
@@ -112,7 +125,7 @@ PG_HD float scrambledRadicalInverseBase(unsigned base, const unsigned short *per
 }
 
 // HaltonSampler::SampleDimension, halton.cpp:118-127
-PG_HD float haltonSample(const HaltonParams &h, long long index, int dim) {
+PG_HD_NOINLINE float haltonSample(const HaltonParams &h, long long index, int dim) {
     if (h.sampleAtPixelCenter && (dim == 0 || dim == 1)) return 0.5f;
     if (dim == 0) {
         unsigned long long a = (unsigned long long)(index >> h.baseExponents[0]);
@@ -120,7 +133,7 @@ PG_HD float haltonSample(const HaltonParams &h, long long index, int dim) {
     }
     if (dim == 1) return radicalInverseBase(3u, (unsigned long long)(index / h.baseScales[1]));
     unsigned base = (unsigned)PG_LD(h.primes + dim);
-    return scrambledRadicalInverseBase(base, h.perms + PG_LD(h.primeSums + dim), (unsigned long long)index);
+    return scrambledRadicalInverseBase(base, PG_LD(h.primeMagic + dim), h.perms + PG_LD(h.primeSums + dim), (unsigned long long)index);
 }
 
 // HaltonSampler's constructor (halton.cpp:65-93): scales/exponents that cover
@@ -161,6 +174,7 @@ inline HaltonParams makeHaltonParams(const int sampleBounds[4], int sampleAtPixe
     h.sampleAtPixelCenter = sampleAtPixelCenter;
     h.primes = nullptr;
     h.primeSums = nullptr;
+    h.primeMagic = nullptr;
     h.perms = nullptr;
     return h;
 }

@@ -119,7 +119,7 @@ PG_HD M44 loadM44(const float *m) {
 
 // ---- AAPlaneShape::Intersect test part, shapes/plane.cpp:15-31.  Note: no
 // t > 0 test (hits behind the origin are accepted) and strict bounds.
-PG_HD bool aaplaneTest(const Ray &ray, const float *rec, float *tOut, V3 *pHitObj) {
+PG_HD_NOINLINE bool aaplaneTest(const Ray &ray, const float *rec, float *tOut, V3 *pHitObj) {
     PlaneParams pl = loadPlane(rec);
     M44 w2o = loadM44(rec + 32);
     V3 oErr, dErr;
@@ -214,7 +214,7 @@ PG_HD SphereParams loadSphere(const float *rec) {
 
 // ---- Sphere::Intersect / IntersectP test part, shapes/sphere.cpp:49-104 and
 // 158-215.  Outputs t, the refined object-space hit point and phi.
-PG_HD bool sphereTest(const Ray &r, const float *rec, float *tOut, V3 *pHitObj, float *phiOut, Ray *rayObj) {
+PG_HD_NOINLINE bool sphereTest(const Ray &r, const float *rec, float *tOut, V3 *pHitObj, float *phiOut, Ray *rayObj) {
     SphereParams sp = loadSphere(rec);
     M44 w2o = loadM44(rec + 32);
     V3 oErr, dErr;

@@ -74,6 +74,9 @@ int pbrtgpu_create(int cuda_device, pbrtgpu_ctx **out) {
         if ((e = cudaMalloc((void **)&ctx->dTotals, 5 * sizeof(unsigned long long))) != cudaSuccess) return bail(e, "cudaMalloc(totals)");
         cudaMemcpy(ctx->dPrimes, primes.data(), primes.size() * sizeof(int), cudaMemcpyHostToDevice);
         cudaMemcpy(ctx->dPrimeSums, sums.data(), primes.size() * sizeof(int), cudaMemcpyHostToDevice);
+        std::vector<unsigned long long> magic = primeMagics(primes);
+        if ((e = cudaMalloc((void **)&ctx->dPrimeMagic, magic.size() * 8)) != cudaSuccess) return bail(e, "cudaMalloc(primeMagic)");
+        cudaMemcpy(ctx->dPrimeMagic, magic.data(), magic.size() * 8, cudaMemcpyHostToDevice);
     }
     *out = ctx;
     return PBRTGPU_OK;
@@ -89,6 +92,7 @@ void pbrtgpu_destroy(pbrtgpu_ctx *ctx) {
     if (ctx->dPerms) cudaFree(ctx->dPerms);
     if (ctx->dPrimes) cudaFree(ctx->dPrimes);
     if (ctx->dPrimeSums) cudaFree(ctx->dPrimeSums);
+    if (ctx->dPrimeMagic) cudaFree(ctx->dPrimeMagic);
     if (ctx->dTotals) cudaFree(ctx->dTotals);
     if (ctx->dTraversalCounts) cudaFree(ctx->dTraversalCounts);
     for (auto &b : ctx->wave)
@@ -161,6 +165,9 @@ int pbrtgpu_upload_scene(pbrtgpu_ctx *ctx, const pbrtgpu_scene *s) {
         if (s->light_tag[i] == PBRTGPU_LIGHT_INFINITE) finishInfiniteLight(lightParams.data() + (size_t)i * PBRTGPU_LIGHT_STRIDE);
     UP(lightParams.data(), lightParams.size(), &d.lightParams);
     ctx->hasNullMaterial = false;
+    ctx->hasInfiniteLight = false;
+    for (int i = 0; i < s->n_lights; ++i)
+        if (s->light_tag[i] == PBRTGPU_LIGHT_INFINITE) ctx->hasInfiniteLight = true;
     if (s->prim_material)
         for (int i = 0; i < s->n_prims; ++i)
             if (s->prim_material[i] < 0) ctx->hasNullMaterial = true;

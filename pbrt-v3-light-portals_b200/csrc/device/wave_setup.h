@@ -72,10 +72,10 @@ inline BatchPlan planBatches(const pbrtgpu_render_params *rp, long long targetSl
 // Bytes per slot of each wave buffer, in the order render.cu / hostsim bind them.
 enum WaveBuf {
     WB_HINDEX, WB_DIM, WB_L, WB_BETA, WB_FLAGS, WB_PFILM, WB_RAYS0, WB_RAYS1, WB_Q0, WB_Q1, WB_HITS, WB_SHADOW_RAYS,
-    WB_SHADOW_CONTRIB, WB_NEE_RAYS, WB_NEE_CONTRIB, WB_NEE_INFO, WB_NEE_HITS, WB_SHADOW_OCC, WB_COUNT
+    WB_SHADOW_CONTRIB, WB_NEE_RAYS, WB_NEE_CONTRIB, WB_NEE_INFO, WB_NEE_HITS, WB_SHADOW_OCC, WB_HIT_IDX, WB_MISS_IDX, WB_COUNT
 };
 inline size_t waveBufBytesPerSlot(int b) {
-    static const size_t sz[WB_COUNT] = {8, 4, 16, 16, 4, 8, 32, 32, 4, 4, 16, 32, 16, 32, 16, 8, 16, 1};
+    static const size_t sz[WB_COUNT] = {8, 4, 16, 16, 4, 8, 32, 32, 4, 4, 16, 32, 16, 32, 16, 8, 16, 1, 4, 4};
     return sz[b];
 }
 inline void bindWaveBuffers(WaveParams *w, void *const bufs[WB_COUNT]) {
@@ -97,6 +97,8 @@ inline void bindWaveBuffers(WaveParams *w, void *const bufs[WB_COUNT]) {
     w->neeInfo = (int *)bufs[WB_NEE_INFO];
     w->neeHits = (F4 *)bufs[WB_NEE_HITS];
     w->shadowOcc = (unsigned char *)bufs[WB_SHADOW_OCC];
+    w->hitIdx = (int *)bufs[WB_HIT_IDX];
+    w->missIdx = (int *)bufs[WB_MISS_IDX];
 }
 
 }  // namespace pg

@@ -126,7 +126,8 @@ extern "C" int hostsim_render(void *p, const pbrtgpu_render_params *rp, float *f
     memset(&w, 0, sizeof(w));
     fillWaveParams(rp, &w);
     w.sc = sc;
-    w.hal.primes = primes.data(), w.hal.primeSums = sums.data(), w.hal.perms = perms.data();
+    std::vector<unsigned long long> magic = primeMagics(primes);
+    w.hal.primes = primes.data(), w.hal.primeSums = sums.data(), w.hal.perms = perms.data(), w.hal.primeMagic = magic.data();
     BatchPlan pl = planBatches(rp, 1 << 18, nullMat);
     const int *cb = rp->cropped_bounds;
     size_t nPix = (size_t)(cb[2] - cb[0]) * (cb[3] - cb[1]);
@@ -160,10 +161,15 @@ extern "C" int hostsim_render(void *p, const pbrtgpu_render_params *rp, float *f
                         Ray ray = loadRay(w.rays[cur], (int)i);
                         Hit h;
                         traverse<false>(w.sc.bvh, ray, &h);
-                        w.hits[i] = f4(bitsToFloat((unsigned)h.prim), h.b0, h.b1, h.b2);
+                        if (h.prim >= 0) {
+                            w.hits[i] = f4(bitsToFloat((unsigned)h.prim), h.b0, h.b1, h.b2);
+                            w.hitIdx[atomicIncInt(&cnt.nHit[d])] = (int)i;
+                        } else
+                            w.missIdx[atomicIncInt(&cnt.nMiss[d])] = (int)i;
                     }
                 });
-                parallelFor(n, threads, [&](int64_t a, int64_t b) { for (int64_t i = a; i < b; ++i) stageShade(w, d, cur, (int)i); });
+                parallelFor(cnt.nMiss[d], threads, [&](int64_t a, int64_t b) { for (int64_t i = a; i < b; ++i) stageMiss(w, cur, w.missIdx[i]); });
+                parallelFor(cnt.nHit[d], threads, [&](int64_t a, int64_t b) { for (int64_t i = a; i < b; ++i) stageShade(w, d, cur, w.hitIdx[i]); });
                 parallelFor(cnt.nShadow[d], threads, [&](int64_t a, int64_t b) {
                     for (int64_t i = a; i < b; ++i) {
                         Ray ray = loadRay(w.shadowRays, (int)i);
@@ -200,6 +206,7 @@ extern "C" int hostsim_render(void *p, const pbrtgpu_render_params *rp, float *f
 extern "C" int hostsim_halton(const pbrtgpu_render_params *rp, const int32_t *xy, const int64_t *num, const int32_t *dim, int64_t n, float *out) {
     static std::vector<int> primes = firstPrimes(), sums;
     static std::vector<uint16_t> perms;
+    static std::vector<unsigned long long> magic = primeMagics(primes);
     if (sums.empty()) {
         sums.resize(primes.size());
         int acc = 0;
@@ -207,7 +214,7 @@ extern "C" int hostsim_halton(const pbrtgpu_render_params *rp, const int32_t *xy
         perms = radicalInversePermutations(primes);
     }
     HaltonParams h = makeHaltonParams(rp->sample_bounds, rp->sample_at_pixel_center);
-    h.primes = primes.data(), h.primeSums = sums.data(), h.perms = perms.data();
+    h.primes = primes.data(), h.primeSums = sums.data(), h.perms = perms.data(), h.primeMagic = magic.data();
     for (int64_t i = 0; i < n; ++i)
         out[i] = haltonSample(h, haltonPixelOffset(h, xy[2 * i], xy[2 * i + 1]) + num[i] * h.sampleStride, dim[i]);
     return 0;

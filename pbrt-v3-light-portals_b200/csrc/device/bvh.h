@@ -96,6 +96,7 @@ template <bool ANY, bool COUNT = false>
 PG_HD bool traverse(const DevBVH &bvh, Ray &ray, Hit *hit, TraverseCounters *cnt = nullptr) {
     V3 invDir = v3(1 / ray.d.x, 1 / ray.d.y, 1 / ray.d.z);
     int dirIsNeg[3] = {invDir.x < 0, invDir.y < 0, invDir.z < 0};
+    RayShear shear = rayShear(ray.d);
     int stackRef[64];
     float stackT[64];
     int sp = 0;
@@ -136,7 +137,7 @@ PG_HD bool traverse(const DevBVH &bvh, Ray &ray, Hit *hit, TraverseCounters *cnt
                 bool h;
                 if (type == 0) {
                     F4 b = PG_LDG(tp + 1), c = PG_LDG(tp + 2);
-                    h = triangleTest(ray, v3(a.x, a.y, a.z), v3(b.x, b.y, b.z), v3(c.x, c.y, c.z), &t, &b0, &b1, &b2);
+                    h = triangleTestSheared(ray, shear, v3(a.x, a.y, a.z), v3(b.x, b.y, b.z), v3(c.x, c.y, c.z), &t, &b0, &b1, &b2);
                     if (!ANY && (tag & kTagDegenerate)) h = false;
                 } else if (type == 1) {
                     h = aaplaneTest(ray, bvh.planeParams + 48 * (size_t)(tag >> kTagShapeShift), &t, nullptr);

@@ -49,6 +49,12 @@ struct pbrtgpu_ctx {
     pg::DeviceBuffer scratch[16];
     pg::DeviceBuffer film;
     int smCount = 148;
+    // trace kernel variant (tuning knobs, env PBRTGPU_TRACE_PERSISTENT / _FETCH_THRESHOLD / _PERSIST_BLOCKS)
+    bool tracePersistent = true;
+    bool shadeSync = false;
+    int fetchThreshold = 8;
+    int persistBlocksPerSM = 8;
+    int *dFetch = nullptr;  // queue cursor of the ray-batch entry points
     long long launches = 0;
 
     int fail(int code, const char *fmt, ...) {

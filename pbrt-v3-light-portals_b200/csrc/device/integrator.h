@@ -21,6 +21,7 @@ struct WaveCounters {
     int nNee[kMaxDepthSlots];         // closest-hit NEE rays generated at depth d
     int nHit[kMaxDepthSlots];         // of the nActive[d] rays: how many hit something (queue hitIdx) ...
     int nMiss[kMaxDepthSlots];        // ... and how many escaped (queue missIdx)
+    int fetch[3][kMaxDepthSlots];     // persistent trace kernels: next unclaimed queue position {closest, shadow, nee}
     unsigned long long cameraRays, closestRays, shadowRays, scrubbed;
 };
 
@@ -65,6 +66,7 @@ struct WaveParams {
     F4 *neeHits;
     unsigned char *shadowOcc;
     WaveCounters *cnt;
+    int fetchThreshold;    // persistent trace kernels refill a warp when this many lanes are idle
     unsigned long long *countTraversal;  // profile mode: {closest, shadow, nee} x {node tests, prim tests}; else null
 };
 

@@ -22,6 +22,7 @@
 #include "ctx.h"
 #include "integrator.h"
 #include "kernels.h"
+#include "trace_persistent.h"
 
 using namespace pg;
 
@@ -62,10 +63,63 @@ __global__ void __launch_bounds__(kTraceBlock) k_trace_closest(WaveParams w, int
     flushCounts<COUNT>(w, 0, c);
 }
 
+// Persistent variants (trace_persistent.h): same results, rays handed to lanes dynamically.
+template <bool COUNT>
+__global__ void __launch_bounds__(kTraceBlock) k_ptrace_closest(WaveParams w, int depth, int cur) {
+    TraverseCounters c = {0, 0};
+    tracePersistent<false, COUNT>(w.sc.bvh, w.rays[cur], w.cnt->nActive[depth], &w.cnt->fetch[0][depth], w.fetchThreshold, &c,
+                                  [&](int i, const Ray &, const Hit &h, bool found) {
+                                      if (found) {
+                                          w.hits[i] = f4(__int_as_float(h.prim), h.b0, h.b1, h.b2);
+                                          w.hitIdx[atomicIncInt(&w.cnt->nHit[depth])] = i;
+                                      } else
+                                          w.missIdx[atomicIncInt(&w.cnt->nMiss[depth])] = i;
+                                  });
+    flushCounts<COUNT>(w, 0, c);
+}
+
+template <bool COUNT>
+__global__ void __launch_bounds__(kTraceBlock) k_ptrace_shadow(WaveParams w, int depth) {
+    TraverseCounters c = {0, 0};
+    tracePersistent<true, COUNT>(w.sc.bvh, w.shadowRays, w.cnt->nShadow[depth], &w.cnt->fetch[1][depth], w.fetchThreshold, &c,
+                                 [&](int i, const Ray &, const Hit &, bool occluded) { stageShadowResolve(w, i, occluded); });
+    flushCounts<COUNT>(w, 1, c);
+}
+
+template <bool COUNT>
+__global__ void __launch_bounds__(kTraceBlock) k_ptrace_nee(WaveParams w, int depth) {
+    TraverseCounters c = {0, 0};
+    tracePersistent<false, COUNT>(w.sc.bvh, w.neeRays, w.cnt->nNee[depth], &w.cnt->fetch[2][depth], w.fetchThreshold, &c,
+                                  [&](int i, const Ray &, const Hit &h, bool) {
+                                      w.neeHits[i] = f4(__int_as_float(h.prim), h.b0, h.b1, h.b2);
+                                  });
+    flushCounts<COUNT>(w, 2, c);
+}
+
+// the emitter lookup / MIS weight of the rays k_ptrace_nee traced
+__global__ void __launch_bounds__(kStageBlock) k_nee_resolve(WaveParams w, int depth) {
+    int n = w.cnt->nNee[depth];
+    int stride = gridDim.x * blockDim.x;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) stageNeeResolve(w, i);
+}
+
 __global__ void __launch_bounds__(kStageBlock) k_shade(WaveParams w, int depth, int cur) {
     int n = w.cnt->nHit[depth];
     int stride = gridDim.x * blockDim.x;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) stageShade(w, depth, cur, w.hitIdx[i]);
+}
+
+// experiment: one 384-thread block per SM, re-synchronised at every vertex so that the warps of an SM
+// walk the (large) shading code together and share instruction-cache lines
+constexpr int kShadeSyncBlock = 384;
+__global__ void __launch_bounds__(kShadeSyncBlock, 1) k_shade_sync(WaveParams w, int depth, int cur) {
+    int n = w.cnt->nHit[depth];
+    int stride = gridDim.x * blockDim.x;
+    for (int base = blockIdx.x * blockDim.x; base < n; base += stride) {
+        int i = base + threadIdx.x;
+        __syncthreads();
+        if (i < n) stageShade(w, depth, cur, w.hitIdx[i]);
+    }
 }
 
 // escaped rays: only launched when the scene has an infinite light
@@ -120,7 +174,8 @@ __global__ void k_batch_stats(WaveCounters *cnt, unsigned long long *totals, int
     totals[2] += shadow;
     totals[3] += cnt->scrubbed;
     for (int d = 0; d <= kMaxDepthSlots; ++d) cnt->nActive[d] = 0;
-    for (int d = 0; d < kMaxDepthSlots; ++d) cnt->nShadow[d] = cnt->nNee[d] = cnt->nHit[d] = cnt->nMiss[d] = 0;
+    for (int d = 0; d < kMaxDepthSlots; ++d)
+        cnt->nShadow[d] = cnt->nNee[d] = cnt->nHit[d] = cnt->nMiss[d] = cnt->fetch[0][d] = cnt->fetch[1][d] = cnt->fetch[2][d] = 0;
     cnt->scrubbed = 0;
 }
 

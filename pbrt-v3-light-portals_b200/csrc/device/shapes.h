@@ -14,21 +14,34 @@ struct Ray {
     float tMax;
 };
 
+// The shear that takes the ray to +z depends on the ray alone; the traversal
+// computes it once per ray instead of once per triangle (same values).
+struct RayShear {
+    int kx, ky, kz;
+    float Sx, Sy, Sz;
+};
+PG_HD RayShear rayShear(V3 rd) {
+    RayShear s;
+    s.kz = maxDimension(vabs(rd));
+    s.kx = s.kz + 1;
+    if (s.kx == 3) s.kx = 0;
+    s.ky = s.kx + 1;
+    if (s.ky == 3) s.ky = 0;
+    V3 d = permute(rd, s.kx, s.ky, s.kz);
+    s.Sx = -d.x / d.z, s.Sy = -d.y / d.z, s.Sz = 1.f / d.z;
+    return s;
+}
+
 // ---- Triangle::Intersect / IntersectP test part, shapes/triangle.cpp:199-292
 // (identical in 427-520).  Returns true when the hit is accepted for
 // ray.tMax; does not update tMax.
-PG_HD bool triangleTest(const Ray &ray, V3 p0, V3 p1, V3 p2, float *tOut, float *b0Out, float *b1Out, float *b2Out = nullptr) {
+PG_HD bool triangleTestSheared(const Ray &ray, const RayShear &sh, V3 p0, V3 p1, V3 p2, float *tOut, float *b0Out, float *b1Out,
+                               float *b2Out = nullptr) {
     V3 p0t = p0 - ray.o, p1t = p1 - ray.o, p2t = p2 - ray.o;
-    int kz = maxDimension(vabs(ray.d));
-    int kx = kz + 1;
-    if (kx == 3) kx = 0;
-    int ky = kx + 1;
-    if (ky == 3) ky = 0;
-    V3 d = permute(ray.d, kx, ky, kz);
-    p0t = permute(p0t, kx, ky, kz);
-    p1t = permute(p1t, kx, ky, kz);
-    p2t = permute(p2t, kx, ky, kz);
-    float Sx = -d.x / d.z, Sy = -d.y / d.z, Sz = 1.f / d.z;
+    p0t = permute(p0t, sh.kx, sh.ky, sh.kz);
+    p1t = permute(p1t, sh.kx, sh.ky, sh.kz);
+    p2t = permute(p2t, sh.kx, sh.ky, sh.kz);
+    float Sx = sh.Sx, Sy = sh.Sy, Sz = sh.Sz;
     p0t.x += Sx * p0t.z;
     p0t.y += Sy * p0t.z;
     p1t.x += Sx * p1t.z;
@@ -77,6 +90,10 @@ PG_HD bool triangleTest(const Ray &ray, V3 p0, V3 p1, V3 p2, float *tOut, float 
     *b1Out = b1;
     if (b2Out) *b2Out = b2;
     return true;
+}
+
+PG_HD bool triangleTest(const Ray &ray, V3 p0, V3 p1, V3 p2, float *tOut, float *b0Out, float *b1Out, float *b2Out = nullptr) {
+    return triangleTestSheared(ray, rayShear(ray.d), p0, p1, p2, tOut, b0Out, b1Out, b2Out);
 }
 
 // ---- Ray to object space with error bounds, transform.h:402-414

@@ -1,8 +1,11 @@
 // Ray-batch entry points: BVHAccel::Intersect / IntersectP over device ray
 // buffers (config C5 and the tier-1 parity tests), plus the trace kernels the
 // wavefront renderer reuses.
+#include <algorithm>
+
 #include "ctx.h"
 #include "kernels.h"
+#include "trace_persistent.h"
 
 using namespace pg;
 
@@ -42,6 +45,25 @@ __global__ void __launch_bounds__(kTraceBlock) k_intersect_any(DevScene sc, cons
     }
 }
 
+// Persistent variants (trace_persistent.h); `rays` / outputs already offset to the chunk, n < 2^31.
+__global__ void __launch_bounds__(kTraceBlock) k_pintersect_closest(DevScene sc, const float4 *__restrict__ rays, int n,
+                                                                    float4 *__restrict__ hits, int *next, int fetchThreshold) {
+    tracePersistent<false, false>(sc.bvh, rays, n, next, fetchThreshold, nullptr, [&](int i, const Ray &ray, const Hit &h, bool found) {
+        float4 out;
+        out.x = __int_as_float(found ? __ldg(sc.primOrigId + h.prim) : -1);
+        out.y = ray.tMax;
+        out.z = found ? h.b0 : 0.f;
+        out.w = found ? h.b1 : 0.f;
+        hits[i] = out;
+    });
+}
+
+__global__ void __launch_bounds__(kTraceBlock) k_pintersect_any(DevScene sc, const float4 *__restrict__ rays, int n,
+                                                                unsigned char *__restrict__ occluded, int *next, int fetchThreshold) {
+    tracePersistent<true, false>(sc.bvh, rays, n, next, fetchThreshold, nullptr,
+                                 [&](int i, const Ray &, const Hit &, bool occ) { occluded[i] = occ ? 1 : 0; });
+}
+
 int traceGrid(const pbrtgpu_ctx *ctx, long long n) {
     long long blocks = (n + kTraceBlock - 1) / kTraceBlock;
     long long cap = (long long)ctx->smCount * kTraceBlocksPerSM;
@@ -59,9 +81,24 @@ static int timedLaunch(pbrtgpu_ctx *ctx, bool any, const void *dRays, long long 
         PG_CUDA(ctx, cudaEventCreate(&e1));
         PG_CUDA(ctx, cudaEventRecord(e0, ctx->stream));
     }
-    int grid = traceGrid(ctx, n);
-    if (any) k_intersect_any<<<grid, kTraceBlock, 0, ctx->stream>>>(ctx->scene, (const float4 *)dRays, n, (unsigned char *)dOut);
-    else k_intersect_closest<<<grid, kTraceBlock, 0, ctx->stream>>>(ctx->scene, (const float4 *)dRays, n, (float4 *)dOut);
+    if (ctx->tracePersistent) {
+        const long long kChunk = 1ll << 30;
+        for (long long off = 0; off < n; off += kChunk) {
+            int m = (int)std::min(kChunk, n - off);
+            long long blocks = std::min<long long>(((long long)m + kTraceBlock - 1) / kTraceBlock, (long long)ctx->smCount * ctx->persistBlocksPerSM);
+            PG_CUDA(ctx, cudaMemsetAsync(ctx->dFetch, 0, sizeof(int), ctx->stream));
+            if (any)
+                k_pintersect_any<<<(int)blocks, kTraceBlock, 0, ctx->stream>>>(ctx->scene, (const float4 *)dRays + 2 * off, m,
+                                                                               (unsigned char *)dOut + off, ctx->dFetch, ctx->fetchThreshold);
+            else
+                k_pintersect_closest<<<(int)blocks, kTraceBlock, 0, ctx->stream>>>(ctx->scene, (const float4 *)dRays + 2 * off, m,
+                                                                                   (float4 *)dOut + off, ctx->dFetch, ctx->fetchThreshold);
+        }
+    } else {
+        int grid = traceGrid(ctx, n);
+        if (any) k_intersect_any<<<grid, kTraceBlock, 0, ctx->stream>>>(ctx->scene, (const float4 *)dRays, n, (unsigned char *)dOut);
+        else k_intersect_closest<<<grid, kTraceBlock, 0, ctx->stream>>>(ctx->scene, (const float4 *)dRays, n, (float4 *)dOut);
+    }
     ctx->launches++;
     PG_CUDA(ctx, cudaGetLastError());
     if (ms) {

@@ -1,0 +1,167 @@
+// Persistent-warp BVH traversal with ray replacement (CUDA only).
+//
+// Same visiting order and arithmetic as traverse<> in bvh.h (and therefore as
+// BVHAccel::Intersect / IntersectP, accelerators/bvh.cpp:662-738); only the
+// mapping of rays to lanes differs:
+//   * a warp keeps running until the ray queue is drained; a lane whose ray
+//     has finished picks up the next queued ray (one atomicAdd per warp and
+//     refill) instead of idling until the slowest ray of its warp is done;
+//   * every round of the outer loop each lane descends interior records until
+//     it holds a leaf, then all lanes that hold one run the primitive tests
+//     together ("while-while"), so box tests and triangle tests do not
+//     serialise against each other inside a warp;
+//   * the triangle shear (triangle.cpp:205-222) is computed once per ray.
+// The result of a ray does not depend on which lane traced it or when, so the
+// output is bit-identical to the one-thread-per-ray loop.
+#ifndef PG_DEVICE_TRACE_PERSISTENT_H
+#define PG_DEVICE_TRACE_PERSISTENT_H
+
+#include "bvh.h"
+
+#if defined(__CUDACC__)
+namespace pg {
+
+__device__ __forceinline__ Ray loadRayF4(const F4 *__restrict__ rays, int i) {
+    F4 a = __ldg(rays + 2 * (size_t)i), b = __ldg(rays + 2 * (size_t)i + 1);
+    Ray r;
+    r.o = v3(a.x, a.y, a.z);
+    r.tMax = a.w;
+    r.d = v3(b.x, b.y, b.z);
+    return r;
+}
+
+// sink(idx, ray, hit, found): called once per ray by the lane that finished it.
+// `next` is a device counter that is 0 at launch.  fetchThreshold: refill when
+// at least this many lanes of the warp are idle (1..32).
+template <bool ANY, bool COUNT, class Sink>
+__device__ __forceinline__ void tracePersistent(const DevBVH &bvh, const F4 *__restrict__ rays, int n, int *next,
+                                                int fetchThreshold, TraverseCounters *cnt, Sink sink) {
+    const unsigned kFull = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    int stackRef[64];
+    float stackT[64];
+    int sp = 0, ref = kEmptyRef, idx = -1;
+    Ray ray;
+    ray.o = ray.d = v3(0.f);
+    ray.tMax = 0;
+    V3 invDir = v3(0.f);
+    int dirIsNeg[3] = {0, 0, 0};
+    RayShear shear = {0, 1, 2, 0.f, 0.f, 0.f};
+    Hit hit;
+    hit.prim = -1;
+    hit.t = hit.b0 = hit.b1 = hit.b2 = 0;
+    bool exhausted = false;  // warp-uniform: the queue has been handed out completely
+
+    for (;;) {
+        unsigned idle = __ballot_sync(kFull, ref == kEmptyRef);
+        if (idle) {
+            int nIdle = __popc(idle);
+            if (!exhausted && nIdle >= fetchThreshold) {
+                int leader = __ffs(idle) - 1;
+                int base = 0;
+                if (lane == leader) base = atomicAdd(next, nIdle);
+                base = __shfl_sync(kFull, base, leader);
+                if (ref == kEmptyRef) {
+                    int mine = base + __popc(idle & ((1u << lane) - 1));
+                    if (mine < n) {
+                        idx = mine;
+                        ray = loadRayF4(rays, idx);
+                        invDir = v3(1 / ray.d.x, 1 / ray.d.y, 1 / ray.d.z);
+                        dirIsNeg[0] = invDir.x < 0, dirIsNeg[1] = invDir.y < 0, dirIsNeg[2] = invDir.z < 0;
+                        shear = rayShear(ray.d);
+                        hit.prim = -1;
+                        sp = 0;
+                        ref = 0;
+                    }
+                }
+                exhausted = base + nIdle >= n;
+            }
+            if (exhausted && __all_sync(kFull, ref == kEmptyRef)) return;
+        }
+        if (ref == kEmptyRef) continue;
+
+        // ---- interior records until this lane holds a leaf (or runs out of nodes)
+        while (ref >= 0) {
+            const F4 *nd = bvh.nodes + 4 * (size_t)ref;
+            F4 q0 = __ldg(nd), q1 = __ldg(nd + 1), q2 = __ldg(nd + 2), q3 = __ldg(nd + 3);
+            if (COUNT) cnt->nodes += 2;
+            int ref0 = f2i(q3.x), ref1 = f2i(q3.y), axis = f2i(q3.z);
+            float t0, t1;
+            bool ok0 = ref0 != kEmptyRef && slabPartial(v3(q0.x, q0.y, q0.z), v3(q0.w, q1.x, q1.y), ray.o, invDir, dirIsNeg, &t0);
+            bool ok1 = ref1 != kEmptyRef && slabPartial(v3(q1.z, q1.w, q2.x), v3(q2.y, q2.z, q2.w), ray.o, invDir, dirIsNeg, &t1);
+            bool nearIs1 = (axis == 0 ? dirIsNeg[0] : (axis == 1 ? dirIsNeg[1] : dirIsNeg[2])) != 0;
+            int refNear = nearIs1 ? ref1 : ref0, refFar = nearIs1 ? ref0 : ref1;
+            bool okNear = nearIs1 ? ok1 : ok0, okFar = nearIs1 ? ok0 : ok1;
+            float tNear = nearIs1 ? t1 : t0, tFar = nearIs1 ? t0 : t1;
+            if (okFar) {
+                stackRef[sp] = refFar;
+                stackT[sp] = tFar;
+                ++sp;
+            }
+            if (okNear && tNear < ray.tMax) {
+                ref = refNear;
+            } else {
+                ref = kEmptyRef;
+                while (sp > 0) {
+                    --sp;
+                    if (stackT[sp] < ray.tMax) {
+                        ref = stackRef[sp];
+                        break;
+                    }
+                }
+            }
+        }
+
+        // ---- the leaf's primitives
+        bool occluded = false;
+        if (ref != kEmptyRef) {
+            int slot = ~ref;
+            for (;; ++slot) {
+                const F4 *tp = bvh.tris + 3 * (size_t)slot;
+                F4 a = __ldg(tp);
+                int tag = f2i(a.w);
+                int type = tag & kTagTypeMask;
+                if (COUNT) cnt->prims += 1;
+                float t, b0 = 0, b1 = 0, b2 = 0;
+                bool h;
+                if (type == 0) {
+                    F4 b = __ldg(tp + 1), c = __ldg(tp + 2);
+                    h = triangleTestSheared(ray, shear, v3(a.x, a.y, a.z), v3(b.x, b.y, b.z), v3(c.x, c.y, c.z), &t, &b0, &b1, &b2);
+                    if (!ANY && (tag & kTagDegenerate)) h = false;
+                } else if (type == 1) {
+                    h = aaplaneTest(ray, bvh.planeParams + 48 * (size_t)(tag >> kTagShapeShift), &t, nullptr);
+                } else {
+                    h = sphereTest(ray, bvh.sphereParams + 48 * (size_t)(tag >> kTagShapeShift), &t, nullptr, nullptr, nullptr);
+                }
+                if (h) {
+                    if (ANY) {
+                        occluded = true;
+                        break;
+                    }
+                    ray.tMax = t;
+                    hit.prim = slot;
+                    hit.t = t;
+                    hit.b0 = b0;
+                    hit.b1 = b1;
+                    hit.b2 = b2;
+                }
+                if (tag & kTagLast) break;
+            }
+            ref = kEmptyRef;
+            if (!occluded) {
+                while (sp > 0) {
+                    --sp;
+                    if (stackT[sp] < ray.tMax) {
+                        ref = stackRef[sp];
+                        break;
+                    }
+                }
+            }
+        }
+        if (ref == kEmptyRef) sink(idx, ray, hit, ANY ? occluded : hit.prim >= 0);
+    }
+}
+
+}  // namespace pg
+#endif  // __CUDACC__
+#endif

@@ -1,5 +1,7 @@
 // Context lifetime and scene upload: reference-layout arrays (pbrtgpu_scene)
 // -> device layout (bvh.h).  Host code only; no kernels here.
+#include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -60,6 +62,11 @@ int pbrtgpu_create(int cuda_device, pbrtgpu_ctx **out) {
     if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "cudaStreamCreate");
     ctx->ownStream = true;
     cudaDeviceGetAttribute(&ctx->smCount, cudaDevAttrMultiProcessorCount, cuda_device);
+    if (const char *v = getenv("PBRTGPU_TRACE_PERSISTENT")) ctx->tracePersistent = atoi(v) != 0;
+    if (const char *v = getenv("PBRTGPU_SHADE_SYNC")) ctx->shadeSync = atoi(v) != 0;
+    if (const char *v = getenv("PBRTGPU_FETCH_THRESHOLD")) ctx->fetchThreshold = std::min(32, std::max(1, atoi(v)));
+    if (const char *v = getenv("PBRTGPU_PERSIST_BLOCKS")) ctx->persistBlocksPerSM = std::min(16, std::max(1, atoi(v)));
+    if ((e = cudaMalloc((void **)&ctx->dFetch, sizeof(int))) != cudaSuccess) return bail(e, "cudaMalloc(fetch)");
     // Halton digit permutations (7.4 MB of uint16), generated, not stored
     std::vector<uint16_t> perms = radicalInversePermutations(firstPrimes());
     if ((e = cudaMalloc((void **)&ctx->dPerms, perms.size() * sizeof(uint16_t))) != cudaSuccess) return bail(e, "cudaMalloc(perms)");
@@ -94,6 +101,7 @@ void pbrtgpu_destroy(pbrtgpu_ctx *ctx) {
     if (ctx->dPrimeSums) cudaFree(ctx->dPrimeSums);
     if (ctx->dPrimeMagic) cudaFree(ctx->dPrimeMagic);
     if (ctx->dTotals) cudaFree(ctx->dTotals);
+    if (ctx->dFetch) cudaFree(ctx->dFetch);
     if (ctx->dTraversalCounts) cudaFree(ctx->dTraversalCounts);
     for (auto &b : ctx->wave)
         if (b.p) cudaFree(b.p);

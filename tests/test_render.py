@@ -197,3 +197,29 @@ def test_gpu_render_errors(pkg, gpu):
     p.spp = 0
     with pytest.raises(pkg.PbrtGpuError):
         gpu.render(p)
+
+
+@pytest.mark.gpu
+def test_gpu_portal_estimator_variance_matches_reference(pkg, gpu, golden):
+    """BASELINE.json tier 2, second half: 'the portal estimator's variance at equal spp is no
+    worse than the reference's'.  Variance = mean squared error against a converged image
+    (strategy "light" at 4096 spp, rendered here); it is measured for this library's 16-spp
+    images and for the reference's (tests/golden), strategy by strategy."""
+    conv_scene = pkg.HostScene(text=scene_text("portal_room_light").replace('"integer pixelsamples" [16]', '"integer pixelsamples" [4096]'),
+                               base_dir=os.path.join(ROOT, "tests", "scenes"))
+    assert conv_scene.params.spp == 4096
+    gpu.upload(conv_scene)
+    film, _ = gpu.render(conv_scene.params)
+    conv = conv_scene.film_to_rgb(film).astype(np.float64)
+    mse = {}
+    for strategy in ("light", "portal", "projection"):
+        case = "portal_room_" + strategy
+        hs = load_case(pkg, case)
+        gpu.upload(hs)
+        film, _ = gpu.render(hs.params)
+        ours = float(np.mean((hs.film_to_rgb(film).astype(np.float64) - conv) ** 2))
+        ref = float(np.mean((golden[case].astype(np.float64) - conv) ** 2))
+        mse[strategy] = (ours, ref)
+        assert ours <= ref * (1 + 1e-3), (strategy, ours, ref)
+    # restricting the samples to the portal must pay off in this scene (the emitter is 16 x the hole)
+    assert mse["portal"][0] < mse["light"][0], mse

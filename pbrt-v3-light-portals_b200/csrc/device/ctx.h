@@ -51,8 +51,10 @@ struct pbrtgpu_ctx {
     int smCount = 148;
     // trace kernel variant (tuning knobs, env PBRTGPU_TRACE_PERSISTENT / _FETCH_THRESHOLD / _PERSIST_BLOCKS)
     bool tracePersistent = true;
-    bool shadeSync = false;
+    bool shadeSync = true;
+    int shadeBlock = 768;
     int fetchThreshold = 8;
+    int phaseBias = 16;
     int persistBlocksPerSM = 8;
     int *dFetch = nullptr;  // queue cursor of the ray-batch entry points
     long long launches = 0;

@@ -66,6 +66,7 @@ struct WaveParams {
     F4 *neeHits;
     unsigned char *shadowOcc;
     WaveCounters *cnt;
+    int phaseBias;         // persistent trace kernels: box-test rounds vs primitive-test rounds, see trace_persistent.h
     int fetchThreshold;    // persistent trace kernels refill a warp when this many lanes are idle
     unsigned long long *countTraversal;  // profile mode: {closest, shadow, nee} x {node tests, prim tests}; else null
 };

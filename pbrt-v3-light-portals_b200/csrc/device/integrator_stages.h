@@ -30,82 +30,195 @@ PG_HD void stageMiss(const WaveParams &w, int cur, int pos) {
 // ---- stage 3: one path vertex (the body of path.cpp:81-187 after scene.Intersect found a hit).
 // pos = position in the depth-d closest-hit queue; cur = which of the two
 // ping-pong queues holds depth d.
-PG_HD void stageShade(const WaveParams &w, int depth, int cur, int pos) {
-    int slot = w.qSlot[cur][pos];
-    Ray ray = loadRay(w.rays[cur], pos);
-    F4 hit = w.hits[pos];
-    int prim = f2i(hit.x);
-    F4 Lq = w.L[slot], bq = w.beta[slot];
-    Spec L = spec(Lq.x, Lq.y, Lq.z), beta = spec(bq.x, bq.y, bq.z);
-    float wvl0 = Lq.w, etaScale = bq.w;
-    int flags = w.flags[slot];
-    int bounces = flags & 255;
-    bool specularBounce = (flags >> 8) & 1;
-    const bool found = true;
-    SurfInt it = hitInteraction(w.sc, prim, hit.y, hit.z, hit.w, ray);
-    PG_TRACE("shade d=%d slot=%d prim=%d o=(%.9g %.9g %.9g) d=(%.9g %.9g %.9g) p=(%.9g %.9g %.9g) n=(%g %g %g) bounces=%d\n", depth, slot, prim, ray.o.x, ray.o.y, ray.o.z, ray.d.x, ray.d.y, ray.d.z, it.p.x, it.p.y, it.p.z, it.n.x, it.n.y, it.n.z, bounces);
+//
+// The body is written as a straight sequence of PHASES, each guarded by
+// per-thread predicates, with sync() between them.  On the GPU sync() is
+// __syncthreads(): the shading code is ~300 KB of SASS, ten times the SM's
+// instruction cache, and warps that drift apart in it stall on instruction
+// fetch (ncu: 74 % of stall samples "no instruction", i-cache hit rate 45 %).
+// Keeping the warps of a block inside the same phase makes one warp's fetch
+// serve them all.  Every thread of the block calls this function, `active`
+// or not.  On the CPU (tests/hostsim) sync() does nothing.
+struct NoSync {
+    PG_HD void operator()() const {}
+};
 
-    // emitted light at the vertex (path.cpp:91-96)
-    if (bounces == 0 || specularBounce) L += beta * hitLe(w.sc, prim, it.n, -ray.d);
-    bool alive = found && bounces < w.maxDepth;
-    Ray next;
+template <class Sync>
+PG_HD void stageShadePhased(const WaveParams &w, int depth, int cur, int pos, bool active, Sync sync) {
+    const int flagsNS = BSDF_ALL & ~BSDF_SPECULAR;
+    // ---- phase 0: path state, the hit record -> SurfaceInteraction, emitted light (path.cpp:91-96)
+    int slot = 0, prim = 0, flags = 0, bounces = 0, mat = -1;
+    bool specularBounce = false;
+    Ray ray, next;
+    Spec L = spec(0.f), beta = spec(0.f);
+    float wvl0 = 0, etaScale = 0;
+    SurfInt it;
+    if (active) {
+        slot = w.qSlot[cur][pos];
+        ray = loadRay(w.rays[cur], pos);
+        F4 hit = w.hits[pos];
+        prim = f2i(hit.x);
+        F4 Lq = w.L[slot], bq = w.beta[slot];
+        L = spec(Lq.x, Lq.y, Lq.z), beta = spec(bq.x, bq.y, bq.z);
+        wvl0 = Lq.w, etaScale = bq.w;
+        flags = w.flags[slot];
+        bounces = flags & 255;
+        specularBounce = (flags >> 8) & 1;
+        it = hitInteraction(w.sc, prim, hit.y, hit.z, hit.w, ray);
+        PG_TRACE("shade d=%d slot=%d prim=%d o=(%.9g %.9g %.9g) d=(%.9g %.9g %.9g) p=(%.9g %.9g %.9g) n=(%g %g %g) bounces=%d\n", depth, slot, prim, ray.o.x, ray.o.y, ray.o.z, ray.d.x, ray.d.y, ray.d.z, it.p.x, it.p.y, it.p.z, it.n.x, it.n.y, it.n.z, bounces);
+        if (bounces == 0 || specularBounce) L += beta * hitLe(w.sc, prim, it.n, -ray.d);
+    }
+    bool alive = active && bounces < w.maxDepth;
     if (alive) {
         if (it.wvlsLost) wvl0 = 0.f;  // Transform::operator()(SurfaceInteraction) leaves wvls default-constructed
-        int mat = w.sc.primMaterial ? PG_LD(w.sc.primMaterial + prim) : -1;
-        if (mat < 0) {
-            // no material: skip the boundary, same bounce count (path.cpp:108-113)
-            next = spawnRay(it.p, it.pError, it.n, ray.d);
-        } else {
-            PathSampler smp;
-            smp.index = w.hIndex[slot];
-            smp.dim = w.dim[slot];
-            BSDF bsdf;
-            makeBSDF(it, PG_LD(w.sc.matTag + mat), w.sc.matParams + PBRTGPU_MAT_STRIDE * (size_t)mat, wvl0, &bsdf);
-            if (bsdfNumComponents(bsdf, BSDF_ALL & ~BSDF_SPECULAR) > 0) {
-                NeeRequest nee;
-                sampleOneLight(w.sc, w.hal, smp, it, bsdf, beta, &nee);
-                if (nee.hasShadow) {
-                    int sp = atomicIncInt(&w.cnt->nShadow[depth]);
-                    storeRay(w.shadowRays, sp, nee.shadowRay);
-                    w.shadowContrib[sp] = f4(nee.shadowContrib.r, nee.shadowContrib.g, nee.shadowContrib.b, bitsToFloat((unsigned)slot));
-                }
-                PG_TRACE("  nee shadow=%d closest=%d mode=%d contrib=(%g %g %g) ray o=(%.9g %.9g %.9g) d=(%.9g %.9g %.9g)\n", (int)nee.hasShadow, (int)nee.hasClosest, nee.mode, nee.closestContrib.r, nee.closestContrib.g, nee.closestContrib.b, nee.closestRay.o.x, nee.closestRay.o.y, nee.closestRay.o.z, nee.closestRay.d.x, nee.closestRay.d.y, nee.closestRay.d.z);
-                if (nee.hasClosest) {
-                    int np = atomicIncInt(&w.cnt->nNee[depth]);
-                    storeRay(w.neeRays, np, nee.closestRay);
-                    w.neeContrib[np] = f4(nee.closestContrib.r, nee.closestContrib.g, nee.closestContrib.b, bitsToFloat((unsigned)slot));
-                    w.neeInfo[2 * (size_t)np] = nee.light;
-                    w.neeInfo[2 * (size_t)np + 1] = nee.mode;
-                }
-            }
-            // sample the BSDF for the next direction (path.cpp:131-151)
-            V3 wo = -ray.d, wi = v3(0, 0, 0);
-            float pdf, u0, u1;
-            int sampled;
-            get2D(w.hal, smp, &u0, &u1);
-            Spec f = bsdfSampleF(bsdf, wo, &wi, u0, u1, &pdf, BSDF_ALL, &sampled);
-            if (isBlack(f) || pdf == 0.f) alive = false;
-            else {
-                beta *= f * absDot(wi, it.ns) / pdf;
-                specularBounce = (sampled & BSDF_SPECULAR) != 0;
-                if ((sampled & BSDF_SPECULAR) && (sampled & BSDF_TRANSMISSION)) {
-                    float eta = bsdf.eta;
-                    etaScale *= (dot(wo, it.n) > 0) ? (eta * eta) : 1 / (eta * eta);
-                }
-                next = spawnRay(it.p, it.pError, it.n, wi);
-                // Russian roulette (path.cpp:177-184)
-                Spec rrBeta = beta * etaScale;
-                if (maxComponentValue(rrBeta) < w.rrThreshold && bounces > 3) {
-                    float q = maxf(.05f, 1 - maxComponentValue(rrBeta));
-                    if (get1D(w.hal, smp) < q) alive = false;
-                    else beta /= 1 - q;
-                }
-                ++bounces;
-            }
-            w.dim[slot] = smp.dim;
+        mat = w.sc.primMaterial ? PG_LD(w.sc.primMaterial + prim) : -1;
+        // no material: skip the boundary, same bounce count (path.cpp:108-113)
+        if (mat < 0) next = spawnRay(it.p, it.pError, it.n, ray.d);
+    }
+    const bool scatter = alive && mat >= 0;
+    sync();
+
+    // ---- phase 1: the material's BSDF (path.cpp:106-107)
+    PathSampler smp;
+    smp.index = 0, smp.dim = 0;
+    BSDF bsdf;
+    bsdf.nLobes = 0;
+    if (scatter) {
+        smp.index = w.hIndex[slot];
+        smp.dim = w.dim[slot];
+        makeBSDF(it, PG_LD(w.sc.matTag + mat), w.sc.matParams + PBRTGPU_MAT_STRIDE * (size_t)mat, wvl0, &bsdf);
+    }
+    sync();
+
+    // ---- phase 2: UniformSampleOneLight's samples and light pick (integrator.cpp:100-122)
+    bool nee = scatter && bsdfNumComponents(bsdf, flagsNS) > 0 && w.sc.nLights > 0;
+    int li = 0, lightTag = 0;
+    float pickPdf = 0, uL0 = 0, uL1 = 0, uS0 = 0, uS1 = 0;
+    if (nee) {
+        float uPick = get1D(w.hal, smp);
+        li = findIntervalCdf(w.sc.lightCdf, w.sc.nLights + 1, uPick);
+        pickPdf = (w.sc.lightFuncInt > 0) ? PG_LD(w.sc.lightFunc + li) / (w.sc.lightFuncInt * w.sc.nLights) : 0;
+        if (pickPdf == 0) nee = false;
+    }
+    if (nee) {
+        get2D(w.hal, smp, &uL0, &uL1);
+        get2D(w.hal, smp, &uS0, &uS1);
+        lightTag = PG_LD(w.sc.lightTag + li);
+    }
+    sync();
+
+    // ---- phase 3: sample the light (EstimateDirect, integrator.cpp:133-141); portal lights take their own estimator
+    const bool portal = nee && lightTag == PBRTGPU_LIGHT_PORTAL_AREA;
+    const bool stock = nee && !portal;
+    const bool isDelta = lightTag == PBRTGPU_LIGHT_POINT || lightTag == PBRTGPU_LIGHT_DISTANT;
+    V3 wi = v3(0, 0, 0);  // Vector3f() is zero-initialised
+    float lightPdf = 0, scatteringPdf = 0;
+    ShapeSample pL;
+    Spec Li = spec(0.f);
+    if (portal) {
+        NeeRequest r;
+        r.hasShadow = r.hasClosest = false;
+        r.light = -1;
+        r.mode = NEE_MIS_LIGHT;
+        estimateDirectPortal(w.sc, li, it, bsdf, uS0, uS1, spec(1.f), &r);
+        if (r.hasClosest) {
+            Spec c = beta * (r.closestContrib / pickPdf);
+            int np = atomicIncInt(&w.cnt->nNee[depth]);
+            storeRay(w.neeRays, np, r.closestRay);
+            w.neeContrib[np] = f4(c.r, c.g, c.b, bitsToFloat((unsigned)slot));
+            w.neeInfo[2 * (size_t)np] = r.light;
+            w.neeInfo[2 * (size_t)np + 1] = r.mode;
         }
     }
-    w.L[slot] = f4(L.r, L.g, L.b, wvl0);
+    if (stock) Li = lightSampleLi(w.sc, li, it, uL0, uL1, &wi, &lightPdf, &pL);
+    sync();
+
+    // ---- phase 4: BSDF value and pdf for the light sample; the shadow ray (integrator.cpp:142-184)
+    if (stock && lightPdf > 0 && !isBlack(Li)) {
+        Spec f = bsdfF(bsdf, it.wo, wi, flagsNS) * absDot(wi, it.ns);
+        scatteringPdf = bsdfPdf(bsdf, it.wo, wi, flagsNS);
+        if (!isBlack(f)) {
+            Spec Ld;
+            if (isDelta) Ld = f * Li / lightPdf;
+            else Ld = f * Li * powerHeuristic(lightPdf, scatteringPdf) / lightPdf;
+            Spec c = beta * (Ld / pickPdf);
+            Ray sr = spawnRayTo(it.p, it.pError, it.n, pL.p, pL.pError, pL.n);
+            int sp = atomicIncInt(&w.cnt->nShadow[depth]);
+            storeRay(w.shadowRays, sp, sr);
+            w.shadowContrib[sp] = f4(c.r, c.g, c.b, bitsToFloat((unsigned)slot));
+        }
+    }
+    sync();
+
+    // ---- phase 5: sample the BSDF for MIS (integrator.cpp:187-207)
+    bool misRay = stock && !isDelta;
+    Spec fMis = spec(0.f);
+    bool sampledSpecular = false;
+    if (misRay) {
+        int sampledType;
+        fMis = bsdfSampleF(bsdf, it.wo, &wi, uS0, uS1, &scatteringPdf, flagsNS, &sampledType);
+        fMis *= absDot(wi, it.ns);
+        sampledSpecular = (sampledType & BSDF_SPECULAR) != 0;
+        misRay = !isBlack(fMis) && scatteringPdf > 0;
+    }
+    sync();
+
+    // ---- phase 6: the light's pdf for that direction; the MIS ray (integrator.cpp:208-254)
+    if (misRay) {
+        float weight = 1;
+        if (!sampledSpecular) {
+            lightPdf = lightPdfLi(w.sc, li, it, wi);
+            if (lightPdf == 0) misRay = false;
+            else weight = powerHeuristic(scatteringPdf, lightPdf);
+        }
+        if (misRay) {
+            Spec c = beta * ((fMis * weight / scatteringPdf) / pickPdf);
+            Ray nr = spawnRay(it.p, it.pError, it.n, wi);
+            int np = atomicIncInt(&w.cnt->nNee[depth]);
+            storeRay(w.neeRays, np, nr);
+            w.neeContrib[np] = f4(c.r, c.g, c.b, bitsToFloat((unsigned)slot));
+            w.neeInfo[2 * (size_t)np] = li;
+            w.neeInfo[2 * (size_t)np + 1] = NEE_MIS_LIGHT;
+        }
+    }
+    sync();
+
+    // ---- phase 7: sample the BSDF for the next direction (path.cpp:131-151)
+    V3 wo = v3(0, 0, 0);
+    float pdf = 0;
+    int sampled = 0;
+    Spec f = spec(0.f);
+    if (scatter) {
+        wo = -ray.d;
+        wi = v3(0, 0, 0);
+        float u0, u1;
+        get2D(w.hal, smp, &u0, &u1);
+        f = bsdfSampleF(bsdf, wo, &wi, u0, u1, &pdf, BSDF_ALL, &sampled);
+    }
+    sync();
+
+    // ---- phase 8: throughput, Russian roulette (path.cpp:177-184), the next ray
+    if (scatter) {
+        if (isBlack(f) || pdf == 0.f) alive = false;
+        else {
+            beta *= f * absDot(wi, it.ns) / pdf;
+            specularBounce = (sampled & BSDF_SPECULAR) != 0;
+            if ((sampled & BSDF_SPECULAR) && (sampled & BSDF_TRANSMISSION)) {
+                float eta = bsdf.eta;
+                etaScale *= (dot(wo, it.n) > 0) ? (eta * eta) : 1 / (eta * eta);
+            }
+            next = spawnRay(it.p, it.pError, it.n, wi);
+            Spec rrBeta = beta * etaScale;
+            if (maxComponentValue(rrBeta) < w.rrThreshold && bounces > 3) {
+                float q = maxf(.05f, 1 - maxComponentValue(rrBeta));
+                if (get1D(w.hal, smp) < q) alive = false;
+                else beta /= 1 - q;
+            }
+            ++bounces;
+        }
+        w.dim[slot] = smp.dim;
+    }
+    if (active) w.L[slot] = f4(L.r, L.g, L.b, wvl0);
     if (alive) {
         w.beta[slot] = f4(beta.r, beta.g, beta.b, etaScale);
         w.flags[slot] = (flags & ~0x1ff) | bounces | (specularBounce ? 256 : 0);
@@ -114,6 +227,8 @@ PG_HD void stageShade(const WaveParams &w, int depth, int cur, int pos) {
         w.qSlot[cur ^ 1][np] = slot;
     }
 }
+
+PG_HD void stageShade(const WaveParams &w, int depth, int cur, int pos) { stageShadePhased(w, depth, cur, pos, true, NoSync()); }
 
 // ---- stage 4a: shadow rays.  Unoccluded -> the light sample counts.
 PG_HD void stageShadowResolve(const WaveParams &w, int pos, bool occluded) {

@@ -64,32 +64,46 @@ __global__ void __launch_bounds__(kTraceBlock) k_trace_closest(WaveParams w, int
 }
 
 // Persistent variants (trace_persistent.h): same results, rays handed to lanes dynamically.
+// They only record what was hit; queue compaction and the resolve arithmetic run as
+// separate dense kernels (few lanes finish a ray in the same round).
 template <bool COUNT>
 __global__ void __launch_bounds__(kTraceBlock) k_ptrace_closest(WaveParams w, int depth, int cur) {
     TraverseCounters c = {0, 0};
-    tracePersistent<false, COUNT>(w.sc.bvh, w.rays[cur], w.cnt->nActive[depth], &w.cnt->fetch[0][depth], w.fetchThreshold, &c,
-                                  [&](int i, const Ray &, const Hit &h, bool found) {
-                                      if (found) {
-                                          w.hits[i] = f4(__int_as_float(h.prim), h.b0, h.b1, h.b2);
-                                          w.hitIdx[atomicIncInt(&w.cnt->nHit[depth])] = i;
-                                      } else
-                                          w.missIdx[atomicIncInt(&w.cnt->nMiss[depth])] = i;
+    tracePersistent<false, COUNT>(w.sc.bvh, w.rays[cur], w.cnt->nActive[depth], &w.cnt->fetch[0][depth], w.fetchThreshold, w.phaseBias, &c,
+                                  [&](int i, const Ray &, const Hit &h, bool) {
+                                      w.hits[i] = f4(__int_as_float(h.prim), h.b0, h.b1, h.b2);
                                   });
     flushCounts<COUNT>(w, 0, c);
+}
+
+// hit / miss positions of the depth-d queue, in queue order (so that k_shade reads its inputs nearly in order)
+__global__ void __launch_bounds__(kStageBlock) k_split_hits(WaveParams w, int depth, bool wantMiss) {
+    int n = w.cnt->nActive[depth];
+    int stride = gridDim.x * blockDim.x;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        if (__float_as_int(w.hits[i].x) >= 0) w.hitIdx[atomicIncInt(&w.cnt->nHit[depth])] = i;
+        else if (wantMiss) w.missIdx[atomicIncInt(&w.cnt->nMiss[depth])] = i;
+    }
 }
 
 template <bool COUNT>
 __global__ void __launch_bounds__(kTraceBlock) k_ptrace_shadow(WaveParams w, int depth) {
     TraverseCounters c = {0, 0};
-    tracePersistent<true, COUNT>(w.sc.bvh, w.shadowRays, w.cnt->nShadow[depth], &w.cnt->fetch[1][depth], w.fetchThreshold, &c,
-                                 [&](int i, const Ray &, const Hit &, bool occluded) { stageShadowResolve(w, i, occluded); });
+    tracePersistent<true, COUNT>(w.sc.bvh, w.shadowRays, w.cnt->nShadow[depth], &w.cnt->fetch[1][depth], w.fetchThreshold, w.phaseBias, &c,
+                                 [&](int i, const Ray &, const Hit &, bool occluded) { w.shadowOcc[i] = occluded ? 1 : 0; });
     flushCounts<COUNT>(w, 1, c);
+}
+
+__global__ void __launch_bounds__(kStageBlock) k_shadow_resolve(WaveParams w, int depth) {
+    int n = w.cnt->nShadow[depth];
+    int stride = gridDim.x * blockDim.x;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) stageShadowResolve(w, i, w.shadowOcc[i] != 0);
 }
 
 template <bool COUNT>
 __global__ void __launch_bounds__(kTraceBlock) k_ptrace_nee(WaveParams w, int depth) {
     TraverseCounters c = {0, 0};
-    tracePersistent<false, COUNT>(w.sc.bvh, w.neeRays, w.cnt->nNee[depth], &w.cnt->fetch[2][depth], w.fetchThreshold, &c,
+    tracePersistent<false, COUNT>(w.sc.bvh, w.neeRays, w.cnt->nNee[depth], &w.cnt->fetch[2][depth], w.fetchThreshold, w.phaseBias, &c,
                                   [&](int i, const Ray &, const Hit &h, bool) {
                                       w.neeHits[i] = f4(__int_as_float(h.prim), h.b0, h.b1, h.b2);
                                   });
@@ -109,16 +123,19 @@ __global__ void __launch_bounds__(kStageBlock) k_shade(WaveParams w, int depth, 
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) stageShade(w, depth, cur, w.hitIdx[i]);
 }
 
-// experiment: one 384-thread block per SM, re-synchronised at every vertex so that the warps of an SM
-// walk the (large) shading code together and share instruction-cache lines
-constexpr int kShadeSyncBlock = 384;
-__global__ void __launch_bounds__(kShadeSyncBlock, 1) k_shade_sync(WaveParams w, int depth, int cur) {
+// One 384-thread block per SM, all of whose warps walk the phases of stageShadePhased together
+// (__syncthreads between phases): the shading code is far larger than the instruction cache.
+struct BlockSync {
+    __device__ __forceinline__ void operator()() const { __syncthreads(); }
+};
+template <int BLOCK, int PER_SM>
+__global__ void __launch_bounds__(BLOCK, PER_SM) k_shade_sync(WaveParams w, int depth, int cur) {
     int n = w.cnt->nHit[depth];
     int stride = gridDim.x * blockDim.x;
     for (int base = blockIdx.x * blockDim.x; base < n; base += stride) {
         int i = base + threadIdx.x;
-        __syncthreads();
-        if (i < n) stageShade(w, depth, cur, w.hitIdx[i]);
+        bool active = i < n;
+        stageShadePhased(w, depth, cur, active ? w.hitIdx[i] : 0, active, BlockSync());
     }
 }
 

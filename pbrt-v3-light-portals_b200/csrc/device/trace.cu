@@ -47,8 +47,8 @@ __global__ void __launch_bounds__(kTraceBlock) k_intersect_any(DevScene sc, cons
 
 // Persistent variants (trace_persistent.h); `rays` / outputs already offset to the chunk, n < 2^31.
 __global__ void __launch_bounds__(kTraceBlock) k_pintersect_closest(DevScene sc, const float4 *__restrict__ rays, int n,
-                                                                    float4 *__restrict__ hits, int *next, int fetchThreshold) {
-    tracePersistent<false, false>(sc.bvh, rays, n, next, fetchThreshold, nullptr, [&](int i, const Ray &ray, const Hit &h, bool found) {
+                                                                    float4 *__restrict__ hits, int *next, int fetchThreshold, int phaseBias) {
+    tracePersistent<false, false>(sc.bvh, rays, n, next, fetchThreshold, phaseBias, nullptr, [&](int i, const Ray &ray, const Hit &h, bool found) {
         float4 out;
         out.x = __int_as_float(found ? __ldg(sc.primOrigId + h.prim) : -1);
         out.y = ray.tMax;
@@ -59,8 +59,8 @@ __global__ void __launch_bounds__(kTraceBlock) k_pintersect_closest(DevScene sc,
 }
 
 __global__ void __launch_bounds__(kTraceBlock) k_pintersect_any(DevScene sc, const float4 *__restrict__ rays, int n,
-                                                                unsigned char *__restrict__ occluded, int *next, int fetchThreshold) {
-    tracePersistent<true, false>(sc.bvh, rays, n, next, fetchThreshold, nullptr,
+                                                                unsigned char *__restrict__ occluded, int *next, int fetchThreshold, int phaseBias) {
+    tracePersistent<true, false>(sc.bvh, rays, n, next, fetchThreshold, phaseBias, nullptr,
                                  [&](int i, const Ray &, const Hit &, bool occ) { occluded[i] = occ ? 1 : 0; });
 }
 
@@ -89,10 +89,10 @@ static int timedLaunch(pbrtgpu_ctx *ctx, bool any, const void *dRays, long long 
             PG_CUDA(ctx, cudaMemsetAsync(ctx->dFetch, 0, sizeof(int), ctx->stream));
             if (any)
                 k_pintersect_any<<<(int)blocks, kTraceBlock, 0, ctx->stream>>>(ctx->scene, (const float4 *)dRays + 2 * off, m,
-                                                                               (unsigned char *)dOut + off, ctx->dFetch, ctx->fetchThreshold);
+                                                                               (unsigned char *)dOut + off, ctx->dFetch, ctx->fetchThreshold, ctx->phaseBias);
             else
                 k_pintersect_closest<<<(int)blocks, kTraceBlock, 0, ctx->stream>>>(ctx->scene, (const float4 *)dRays + 2 * off, m,
-                                                                                   (float4 *)dOut + off, ctx->dFetch, ctx->fetchThreshold);
+                                                                                   (float4 *)dOut + off, ctx->dFetch, ctx->fetchThreshold, ctx->phaseBias);
         }
     } else {
         int grid = traceGrid(ctx, n);

@@ -6,10 +6,11 @@
 //   * a warp keeps running until the ray queue is drained; a lane whose ray
 //     has finished picks up the next queued ray (one atomicAdd per warp and
 //     refill) instead of idling until the slowest ray of its warp is done;
-//   * every round of the outer loop each lane descends interior records until
-//     it holds a leaf, then all lanes that hold one run the primitive tests
-//     together ("while-while"), so box tests and triangle tests do not
-//     serialise against each other inside a warp;
+//   * every round of the loop the warp does ONE kind of work, chosen by a vote:
+//     either each lane that is at an interior record tests its two children,
+//     or each lane that is at a primitive tests it; box tests and triangle
+//     tests never serialise against each other inside a warp, and a lane waits
+//     only until its kind of work has the majority;
 //   * the triangle shear (triangle.cpp:205-222) is computed once per ray.
 // The result of a ray does not depend on which lane traced it or when, so the
 // output is bit-identical to the one-thread-per-ray loop.
@@ -32,14 +33,17 @@ __device__ __forceinline__ Ray loadRayF4(const F4 *__restrict__ rays, int i) {
 
 // sink(idx, ray, hit, found): called once per ray by the lane that finished it.
 // `next` is a device counter that is 0 at launch.  fetchThreshold: refill when
-// at least this many lanes of the warp are idle (1..32).
+// at least this many lanes of the warp are idle (1..32).  phaseBias (in 1/16):
+// a round runs box tests when 16 * (#lanes at an interior record) >=
+// phaseBias * (#lanes at a primitive), else one primitive test per such lane.
 template <bool ANY, bool COUNT, class Sink>
 __device__ __forceinline__ void tracePersistent(const DevBVH &bvh, const F4 *__restrict__ rays, int n, int *next,
-                                                int fetchThreshold, TraverseCounters *cnt, Sink sink) {
+                                                int fetchThreshold, int phaseBias, TraverseCounters *cnt, Sink sink) {
     const unsigned kFull = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     int stackRef[64];
     float stackT[64];
+    // ref >= 0: interior record to visit; ref < 0: ~ref is the next primitive slot to test; kEmptyRef: no ray
     int sp = 0, ref = kEmptyRef, idx = -1;
     Ray ray;
     ray.o = ray.d = v3(0.f);
@@ -78,66 +82,53 @@ __device__ __forceinline__ void tracePersistent(const DevBVH &bvh, const F4 *__r
             }
             if (exhausted && __all_sync(kFull, ref == kEmptyRef)) return;
         }
-        if (ref == kEmptyRef) continue;
-
-        // ---- interior records until this lane holds a leaf (or runs out of nodes)
-        while (ref >= 0) {
-            const F4 *nd = bvh.nodes + 4 * (size_t)ref;
-            F4 q0 = __ldg(nd), q1 = __ldg(nd + 1), q2 = __ldg(nd + 2), q3 = __ldg(nd + 3);
-            if (COUNT) cnt->nodes += 2;
-            int ref0 = f2i(q3.x), ref1 = f2i(q3.y), axis = f2i(q3.z);
-            float t0, t1;
-            bool ok0 = ref0 != kEmptyRef && slabPartial(v3(q0.x, q0.y, q0.z), v3(q0.w, q1.x, q1.y), ray.o, invDir, dirIsNeg, &t0);
-            bool ok1 = ref1 != kEmptyRef && slabPartial(v3(q1.z, q1.w, q2.x), v3(q2.y, q2.z, q2.w), ray.o, invDir, dirIsNeg, &t1);
-            bool nearIs1 = (axis == 0 ? dirIsNeg[0] : (axis == 1 ? dirIsNeg[1] : dirIsNeg[2])) != 0;
-            int refNear = nearIs1 ? ref1 : ref0, refFar = nearIs1 ? ref0 : ref1;
-            bool okNear = nearIs1 ? ok1 : ok0, okFar = nearIs1 ? ok0 : ok1;
-            float tNear = nearIs1 ? t1 : t0, tFar = nearIs1 ? t0 : t1;
-            if (okFar) {
-                stackRef[sp] = refFar;
-                stackT[sp] = tFar;
-                ++sp;
-            }
-            if (okNear && tNear < ray.tMax) {
-                ref = refNear;
-            } else {
-                ref = kEmptyRef;
-                while (sp > 0) {
-                    --sp;
-                    if (stackT[sp] < ray.tMax) {
-                        ref = stackRef[sp];
-                        break;
-                    }
+        const bool atInterior = ref >= 0, atPrim = ref < 0 && ref != kEmptyRef;
+        int nI = __popc(__ballot_sync(kFull, atInterior)), nP = __popc(__ballot_sync(kFull, atPrim));
+        bool popNext = false, occluded = false;
+        if (nI > 0 && 16 * nI >= phaseBias * nP) {
+            // ---- one interior record: both children's bounds
+            if (atInterior) {
+                const F4 *nd = bvh.nodes + 4 * (size_t)ref;
+                F4 q0 = __ldg(nd), q1 = __ldg(nd + 1), q2 = __ldg(nd + 2), q3 = __ldg(nd + 3);
+                if (COUNT) cnt->nodes += 2;
+                int ref0 = f2i(q3.x), ref1 = f2i(q3.y), axis = f2i(q3.z);
+                float t0, t1;
+                bool ok0 = ref0 != kEmptyRef && slabPartial(v3(q0.x, q0.y, q0.z), v3(q0.w, q1.x, q1.y), ray.o, invDir, dirIsNeg, &t0);
+                bool ok1 = ref1 != kEmptyRef && slabPartial(v3(q1.z, q1.w, q2.x), v3(q2.y, q2.z, q2.w), ray.o, invDir, dirIsNeg, &t1);
+                bool nearIs1 = (axis == 0 ? dirIsNeg[0] : (axis == 1 ? dirIsNeg[1] : dirIsNeg[2])) != 0;
+                int refNear = nearIs1 ? ref1 : ref0, refFar = nearIs1 ? ref0 : ref1;
+                bool okNear = nearIs1 ? ok1 : ok0, okFar = nearIs1 ? ok0 : ok1;
+                float tNear = nearIs1 ? t1 : t0, tFar = nearIs1 ? t0 : t1;
+                if (okFar) {
+                    stackRef[sp] = refFar;
+                    stackT[sp] = tFar;
+                    ++sp;
                 }
+                if (okNear && tNear < ray.tMax) ref = refNear;
+                else popNext = true;
             }
-        }
-
-        // ---- the leaf's primitives
-        bool occluded = false;
-        if (ref != kEmptyRef) {
+        } else if (atPrim) {
+            // ---- one primitive of the leaf
             int slot = ~ref;
-            for (;; ++slot) {
-                const F4 *tp = bvh.tris + 3 * (size_t)slot;
-                F4 a = __ldg(tp);
-                int tag = f2i(a.w);
-                int type = tag & kTagTypeMask;
-                if (COUNT) cnt->prims += 1;
-                float t, b0 = 0, b1 = 0, b2 = 0;
-                bool h;
-                if (type == 0) {
-                    F4 b = __ldg(tp + 1), c = __ldg(tp + 2);
-                    h = triangleTestSheared(ray, shear, v3(a.x, a.y, a.z), v3(b.x, b.y, b.z), v3(c.x, c.y, c.z), &t, &b0, &b1, &b2);
-                    if (!ANY && (tag & kTagDegenerate)) h = false;
-                } else if (type == 1) {
-                    h = aaplaneTest(ray, bvh.planeParams + 48 * (size_t)(tag >> kTagShapeShift), &t, nullptr);
-                } else {
-                    h = sphereTest(ray, bvh.sphereParams + 48 * (size_t)(tag >> kTagShapeShift), &t, nullptr, nullptr, nullptr);
-                }
-                if (h) {
-                    if (ANY) {
-                        occluded = true;
-                        break;
-                    }
+            const F4 *tp = bvh.tris + 3 * (size_t)slot;
+            F4 a = __ldg(tp);
+            int tag = f2i(a.w);
+            int type = tag & kTagTypeMask;
+            if (COUNT) cnt->prims += 1;
+            float t, b0 = 0, b1 = 0, b2 = 0;
+            bool h;
+            if (type == 0) {
+                F4 b = __ldg(tp + 1), c = __ldg(tp + 2);
+                h = triangleTestSheared(ray, shear, v3(a.x, a.y, a.z), v3(b.x, b.y, b.z), v3(c.x, c.y, c.z), &t, &b0, &b1, &b2);
+                if (!ANY && (tag & kTagDegenerate)) h = false;
+            } else if (type == 1) {
+                h = aaplaneTest(ray, bvh.planeParams + 48 * (size_t)(tag >> kTagShapeShift), &t, nullptr);
+            } else {
+                h = sphereTest(ray, bvh.sphereParams + 48 * (size_t)(tag >> kTagShapeShift), &t, nullptr, nullptr, nullptr);
+            }
+            if (h) {
+                if (ANY) occluded = true;
+                else {
                     ray.tMax = t;
                     hit.prim = slot;
                     hit.t = t;
@@ -145,20 +136,22 @@ __device__ __forceinline__ void tracePersistent(const DevBVH &bvh, const F4 *__r
                     hit.b1 = b1;
                     hit.b2 = b2;
                 }
-                if (tag & kTagLast) break;
             }
+            if (occluded) ref = kEmptyRef;
+            else if (tag & kTagLast) popNext = true;
+            else ref = ~(slot + 1);
+        }
+        if (popNext) {  // the next stacked node whose entry distance is still inside the ray
             ref = kEmptyRef;
-            if (!occluded) {
-                while (sp > 0) {
-                    --sp;
-                    if (stackT[sp] < ray.tMax) {
-                        ref = stackRef[sp];
-                        break;
-                    }
+            while (sp > 0) {
+                --sp;
+                if (stackT[sp] < ray.tMax) {
+                    ref = stackRef[sp];
+                    break;
                 }
             }
         }
-        if (ref == kEmptyRef) sink(idx, ray, hit, ANY ? occluded : hit.prim >= 0);
+        if ((atInterior || atPrim) && ref == kEmptyRef) sink(idx, ray, hit, ANY ? occluded : hit.prim >= 0);
     }
 }
 

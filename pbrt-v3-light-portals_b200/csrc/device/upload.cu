@@ -65,6 +65,8 @@ int pbrtgpu_create(int cuda_device, pbrtgpu_ctx **out) {
     if (const char *v = getenv("PBRTGPU_TRACE_PERSISTENT")) ctx->tracePersistent = atoi(v) != 0;
     if (const char *v = getenv("PBRTGPU_SHADE_SYNC")) ctx->shadeSync = atoi(v) != 0;
     if (const char *v = getenv("PBRTGPU_FETCH_THRESHOLD")) ctx->fetchThreshold = std::min(32, std::max(1, atoi(v)));
+    if (const char *v = getenv("PBRTGPU_SHADE_BLOCK")) ctx->shadeBlock = atoi(v);
+    if (const char *v = getenv("PBRTGPU_PHASE_BIAS")) ctx->phaseBias = std::min(1024, std::max(0, atoi(v)));
     if (const char *v = getenv("PBRTGPU_PERSIST_BLOCKS")) ctx->persistBlocksPerSM = std::min(16, std::max(1, atoi(v)));
     if ((e = cudaMalloc((void **)&ctx->dFetch, sizeof(int))) != cudaSuccess) return bail(e, "cudaMalloc(fetch)");
     // Halton digit permutations (7.4 MB of uint16), generated, not stored

@@ -229,17 +229,21 @@ def main():
     view = hs.view
     scene_bytes = (view.n_nodes * (24 + 4 + 2 + 1) + view.n_prims * (1 + 1 + 4 * 4 + 36 + (36 if view.tri_n else 0) + (24 if view.tri_uv else 0)))
     e2e_steps = max(2, min(args.steps, 4))
+    film_host = torch.empty((cb[3] - cb[1], cb[2] - cb[0], 4), dtype=torch.float32, pin_memory=True).numpy()  # pinned result buffer
     ctx.upload(hs)
-    ctx.render(params)
+    ctx.render(params, out=film_host)
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
     t0 = time.perf_counter()
+    e2e_step_ms = []
     for k in range(e2e_steps):
+        ts = time.perf_counter()
         params.spp_begin = (k * S * world) % TOTAL_SPP
         params.spp_end = params.spp_begin + S * world
         ctx.upload(hs)
-        film, _ = ctx.render(params)
+        film, _ = ctx.render(params, out=film_host)
+        e2e_step_ms.append(round((time.perf_counter() - ts) * 1e3, 2))
     t_e2e = torch.tensor([time.perf_counter() - t0], device="cuda", dtype=torch.float64)
     if world > 1:
         dist.all_reduce(t_e2e, op=dist.ReduceOp.MAX)
@@ -268,7 +272,7 @@ def main():
     path_rays = pst.closest_rays - pst.nee_closest_rays
     alg_bytes = 48.0 * path_rays + 32.0 * tc["node_tests"] + 48.0 * tc["prim_tests"]
     achieved = alg_bytes / (tc["ms"] / 1e3) / 1e9 if tc["ms"] > 0 else 0.0
-    roofline = {"kernel": "k_trace_closest", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+    roofline = {"kernel": "k_ptrace_closest", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": None, "peak_source": peak_src, "launches": tc["launches"], "avg_launch_ms": tc["ms"] / max(1, tc["launches"]),
                 "node_tests_per_ray": tc["node_tests"] / max(1, path_rays), "prim_tests_per_ray": tc["prim_tests"] / max(1, path_rays),
                 "share_of_step": {k: (p["ms"] / total_ms if total_ms else 0) for k, p in prof.items()}}
@@ -281,7 +285,7 @@ def main():
                       "spp_per_step_per_gpu": S, "l2": "wavefront state of a step (%.0f MB) and the film exceed L2; no flush needed" %
                       (min(samples_per_step // world, 4 << 20) * 270 / 1e6), "rays_per_sample": float(tot[1].item()) / (samples_per_step * args.steps)},
            "gpu_launches": int(tot[0].item()), "clocks": clk,
-           "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(scene_bytes), "d2h_bytes_per_step": int(n_pix * 16), "steps": e2e_steps},
+           "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(scene_bytes), "d2h_bytes_per_step": int(n_pix * 16), "steps": e2e_steps, "step_ms": e2e_step_ms},
            "roofline": roofline}
     if not args.no_cpu_baseline and world == 1:
         cores = os.cpu_count() or 1

@@ -264,10 +264,17 @@ class GpuContext:
         self._check(fn(self._h, C.c_void_p(d_rays_ptr), n, C.c_void_p(d_out_ptr), C.byref(ms)))
         return ms.value
 
-    def render(self, params, want_stats=True):
+    def render(self, params, want_stats=True, out=None):
+        """Integrator::Render: returns (film[h, w, 4] = sum w*X, sum w*Y, sum w*Z, sum w; stats).
+        `out` may be a caller-owned float32 array of that shape (e.g. a view of pinned memory)."""
         cb = params.cropped_bounds
         w, h = cb[2] - cb[0], cb[3] - cb[1]
-        film = np.empty((h, w, 4), np.float32)
+        if out is not None:
+            if out.dtype != np.float32 or out.shape != (h, w, 4) or not out.flags["C_CONTIGUOUS"]:
+                raise ValueError("out must be a C-contiguous float32 array of shape (%d, %d, 4)" % (h, w))
+            film = out
+        else:
+            film = np.empty((h, w, 4), np.float32)
         stats = Stats()
         self._check(self._lib.pbrtgpu_render(self._h, C.byref(params), film.ctypes.data, C.byref(stats)))
         return film, stats

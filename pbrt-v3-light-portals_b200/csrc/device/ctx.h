@@ -11,6 +11,7 @@
 
 #include "../../../include/pbrtgpu.h"
 #include "ctx_scene.h"
+#include "kernels.h"
 
 namespace pg {
 
@@ -28,7 +29,12 @@ struct pbrtgpu_ctx {
     std::string lastError;
     bool haveScene = false;
     pg::DevScene scene;
-    std::vector<void *> sceneAllocs;  // freed on re-upload / destroy
+    struct Block {
+        void *p;
+        size_t bytes;
+    };
+    std::vector<Block> sceneAllocs;  // the scene's device arrays
+    std::vector<Block> scenePool;    // the previous scene's arrays during a re-upload: reused when a size matches
     // Halton tables (uploaded at create)
     unsigned short *dPerms = nullptr;
     unsigned long long *dPrimeMagic = nullptr;
@@ -55,7 +61,7 @@ struct pbrtgpu_ctx {
     int shadeBlock = 768;
     int fetchThreshold = 8;
     int phaseBias = 16;
-    int persistBlocksPerSM = 8;
+    int persistBlocksPerSM = pg::kPersistMinBlocks;
     int *dFetch = nullptr;  // queue cursor of the ray-batch entry points
     long long launches = 0;
 
@@ -85,8 +91,15 @@ int uploadArray(pbrtgpu_ctx *ctx, const T *host, size_t count, const T **dev) {
     *dev = nullptr;
     if (!host || count == 0) return PBRTGPU_OK;
     void *d = nullptr;
-    PG_CUDA(ctx, cudaMalloc(&d, count * sizeof(T)));
-    ctx->sceneAllocs.push_back(d);
+    const size_t bytes = count * sizeof(T);
+    for (size_t i = 0; i < ctx->scenePool.size(); ++i)
+        if (ctx->scenePool[i].bytes == bytes) {
+            d = ctx->scenePool[i].p;
+            ctx->scenePool.erase(ctx->scenePool.begin() + i);
+            break;
+        }
+    if (!d) PG_CUDA(ctx, cudaMalloc(&d, bytes));
+    ctx->sceneAllocs.push_back({d, bytes});
     PG_CUDA(ctx, cudaMemcpyAsync(d, host, count * sizeof(T), cudaMemcpyHostToDevice, ctx->stream));
     *dev = (const T *)d;
     return PBRTGPU_OK;

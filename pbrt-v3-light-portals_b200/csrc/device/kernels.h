@@ -10,6 +10,10 @@ namespace pg {
 // loop over the work (grid-stride), so no tail wave is left partly filled.
 constexpr int kTraceBlock = 128;
 constexpr int kTraceBlocksPerSM = 8;
+#ifndef PG_PERSIST_MIN_BLOCKS
+#define PG_PERSIST_MIN_BLOCKS 6
+#endif
+constexpr int kPersistMinBlocks = PG_PERSIST_MIN_BLOCKS;  // persistent trace kernels: resident blocks per SM the register budget allows
 
 int traceGrid(const pbrtgpu_ctx *ctx, long long n);
 

@@ -67,7 +67,7 @@ __global__ void __launch_bounds__(kTraceBlock) k_trace_closest(WaveParams w, int
 // They only record what was hit; queue compaction and the resolve arithmetic run as
 // separate dense kernels (few lanes finish a ray in the same round).
 template <bool COUNT>
-__global__ void __launch_bounds__(kTraceBlock) k_ptrace_closest(WaveParams w, int depth, int cur) {
+__global__ void __launch_bounds__(kTraceBlock, kPersistMinBlocks) k_ptrace_closest(WaveParams w, int depth, int cur) {
     TraverseCounters c = {0, 0};
     tracePersistent<false, COUNT>(w.sc.bvh, w.rays[cur], w.cnt->nActive[depth], &w.cnt->fetch[0][depth], w.fetchThreshold, w.phaseBias, &c,
                                   [&](int i, const Ray &, const Hit &h, bool) {
@@ -87,7 +87,7 @@ __global__ void __launch_bounds__(kStageBlock) k_split_hits(WaveParams w, int de
 }
 
 template <bool COUNT>
-__global__ void __launch_bounds__(kTraceBlock) k_ptrace_shadow(WaveParams w, int depth) {
+__global__ void __launch_bounds__(kTraceBlock, kPersistMinBlocks) k_ptrace_shadow(WaveParams w, int depth) {
     TraverseCounters c = {0, 0};
     tracePersistent<true, COUNT>(w.sc.bvh, w.shadowRays, w.cnt->nShadow[depth], &w.cnt->fetch[1][depth], w.fetchThreshold, w.phaseBias, &c,
                                  [&](int i, const Ray &, const Hit &, bool occluded) { w.shadowOcc[i] = occluded ? 1 : 0; });
@@ -101,7 +101,7 @@ __global__ void __launch_bounds__(kStageBlock) k_shadow_resolve(WaveParams w, in
 }
 
 template <bool COUNT>
-__global__ void __launch_bounds__(kTraceBlock) k_ptrace_nee(WaveParams w, int depth) {
+__global__ void __launch_bounds__(kTraceBlock, kPersistMinBlocks) k_ptrace_nee(WaveParams w, int depth) {
     TraverseCounters c = {0, 0};
     tracePersistent<false, COUNT>(w.sc.bvh, w.neeRays, w.cnt->nNee[depth], &w.cnt->fetch[2][depth], w.fetchThreshold, w.phaseBias, &c,
                                   [&](int i, const Ray &, const Hit &h, bool) {

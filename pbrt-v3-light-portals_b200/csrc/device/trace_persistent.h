@@ -31,6 +31,29 @@ __device__ __forceinline__ Ray loadRayF4(const F4 *__restrict__ rays, int i) {
     return r;
 }
 
+// slabPartial (bvh.h) without the early returns: the same comparisons and the same
+// conditional updates, combined at the end (values computed past a failed test are unused).
+__device__ __forceinline__ bool slabPartialFlat(V3 bmin, V3 bmax, V3 o, V3 invDir, const bool dirIsNeg[3], float *tMinOut) {
+    const float k = 1 + 2 * gammaf(3);
+    float tMin = ((dirIsNeg[0] ? bmax.x : bmin.x) - o.x) * invDir.x;
+    float tMax = ((dirIsNeg[0] ? bmin.x : bmax.x) - o.x) * invDir.x;
+    float tyMin = ((dirIsNeg[1] ? bmax.y : bmin.y) - o.y) * invDir.y;
+    float tyMax = ((dirIsNeg[1] ? bmin.y : bmax.y) - o.y) * invDir.y;
+    float tzMin = ((dirIsNeg[2] ? bmax.z : bmin.z) - o.z) * invDir.z;
+    float tzMax = ((dirIsNeg[2] ? bmin.z : bmax.z) - o.z) * invDir.z;
+    tMax *= k;
+    tyMax *= k;
+    tzMax *= k;
+    bool missXY = tMin > tyMax || tyMin > tMax;
+    if (tyMin > tMin) tMin = tyMin;
+    if (tyMax < tMax) tMax = tyMax;
+    bool missZ = tMin > tzMax || tzMin > tMax;
+    if (tzMin > tMin) tMin = tzMin;
+    if (tzMax < tMax) tMax = tzMax;
+    *tMinOut = tMin;
+    return !missXY && !missZ && tMax > 0;
+}
+
 // sink(idx, ray, hit, found): called once per ray by the lane that finished it.
 // `next` is a device counter that is 0 at launch.  fetchThreshold: refill when
 // at least this many lanes of the warp are idle (1..32).  phaseBias (in 1/16):
@@ -49,7 +72,9 @@ __device__ __forceinline__ void tracePersistent(const DevBVH &bvh, const F4 *__r
     ray.o = ray.d = v3(0.f);
     ray.tMax = 0;
     V3 invDir = v3(0.f);
-    int dirIsNeg[3] = {0, 0, 0};
+    bool dirIsNeg[3] = {false, false, false};
+    int topRef = 0;    // the top stack entry lives in registers: a pop does not wait for local memory
+    float topT = 0;
     RayShear shear = {0, 1, 2, 0.f, 0.f, 0.f};
     Hit hit;
     hit.prim = -1;
@@ -93,15 +118,19 @@ __device__ __forceinline__ void tracePersistent(const DevBVH &bvh, const F4 *__r
                 if (COUNT) cnt->nodes += 2;
                 int ref0 = f2i(q3.x), ref1 = f2i(q3.y), axis = f2i(q3.z);
                 float t0, t1;
-                bool ok0 = ref0 != kEmptyRef && slabPartial(v3(q0.x, q0.y, q0.z), v3(q0.w, q1.x, q1.y), ray.o, invDir, dirIsNeg, &t0);
-                bool ok1 = ref1 != kEmptyRef && slabPartial(v3(q1.z, q1.w, q2.x), v3(q2.y, q2.z, q2.w), ray.o, invDir, dirIsNeg, &t1);
-                bool nearIs1 = (axis == 0 ? dirIsNeg[0] : (axis == 1 ? dirIsNeg[1] : dirIsNeg[2])) != 0;
+                bool ok0 = ref0 != kEmptyRef && slabPartialFlat(v3(q0.x, q0.y, q0.z), v3(q0.w, q1.x, q1.y), ray.o, invDir, dirIsNeg, &t0);
+                bool ok1 = ref1 != kEmptyRef && slabPartialFlat(v3(q1.z, q1.w, q2.x), v3(q2.y, q2.z, q2.w), ray.o, invDir, dirIsNeg, &t1);
+                bool nearIs1 = axis == 0 ? dirIsNeg[0] : (axis == 1 ? dirIsNeg[1] : dirIsNeg[2]);
                 int refNear = nearIs1 ? ref1 : ref0, refFar = nearIs1 ? ref0 : ref1;
                 bool okNear = nearIs1 ? ok1 : ok0, okFar = nearIs1 ? ok0 : ok1;
                 float tNear = nearIs1 ? t1 : t0, tFar = nearIs1 ? t0 : t1;
                 if (okFar) {
-                    stackRef[sp] = refFar;
-                    stackT[sp] = tFar;
+                    if (sp > 0) {
+                        stackRef[sp - 1] = topRef;
+                        stackT[sp - 1] = topT;
+                    }
+                    topRef = refFar;
+                    topT = tFar;
                     ++sp;
                 }
                 if (okNear && tNear < ray.tMax) ref = refNear;
@@ -145,8 +174,14 @@ __device__ __forceinline__ void tracePersistent(const DevBVH &bvh, const F4 *__r
             ref = kEmptyRef;
             while (sp > 0) {
                 --sp;
-                if (stackT[sp] < ray.tMax) {
-                    ref = stackRef[sp];
+                int r = topRef;
+                float t = topT;
+                if (sp > 0) {
+                    topRef = stackRef[sp - 1];
+                    topT = stackT[sp - 1];
+                }
+                if (t < ray.tMax) {
+                    ref = r;
                     break;
                 }
             }

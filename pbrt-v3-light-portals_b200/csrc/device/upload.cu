@@ -25,8 +25,16 @@ int ensureBuffer(pbrtgpu_ctx *ctx, DeviceBuffer &b, size_t bytes) {
 }
 }  // namespace pg
 
-static void freeScene(pbrtgpu_ctx *ctx) {
-    for (void *p : ctx->sceneAllocs) cudaFree(p);
+static void drainScenePool(pbrtgpu_ctx *ctx) {
+    for (auto &b : ctx->scenePool) cudaFree(b.p);
+    ctx->scenePool.clear();
+}
+// keepForReuse: a re-upload of a scene of the same shape then needs no cudaMalloc / cudaFree
+static void freeScene(pbrtgpu_ctx *ctx, bool keepForReuse = false) {
+    drainScenePool(ctx);
+    if (keepForReuse) ctx->scenePool.swap(ctx->sceneAllocs);
+    else
+        for (auto &b : ctx->sceneAllocs) cudaFree(b.p);
     ctx->sceneAllocs.clear();
     ctx->haveScene = false;
 }
@@ -135,7 +143,7 @@ int pbrtgpu_upload_scene(pbrtgpu_ctx *ctx, const pbrtgpu_scene *s) {
         } else if (s->bvh_offset[i] < 0 || s->bvh_offset[i] + (int)s->bvh_nprims[i] > s->n_prims)
             return ctx->fail(PBRTGPU_ERR_INVALID, "BVH leaf %d: primitive range out of bounds", i);
     }
-    freeScene(ctx);
+    freeScene(ctx, /*keepForReuse=*/true);
     DevScene &d = ctx->scene;
     memset(&d, 0, sizeof(d));
 
@@ -199,6 +207,7 @@ int pbrtgpu_upload_scene(pbrtgpu_ctx *ctx, const pbrtgpu_scene *s) {
     memcpy(d.worldCenter, s->world_center, sizeof(d.worldCenter));
     d.worldRadius = s->world_radius;
     PG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    drainScenePool(ctx);
     ctx->haveScene = true;
     return PBRTGPU_OK;
 }

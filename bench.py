@@ -272,8 +272,13 @@ def main():
     path_rays = pst.closest_rays - pst.nee_closest_rays
     alg_bytes = 48.0 * path_rays + 32.0 * tc["node_tests"] + 48.0 * tc["prim_tests"]
     achieved = alg_bytes / (tc["ms"] / 1e3) / 1e9 if tc["ms"] > 0 else 0.0
+    traffic, traffic_src = None, None
+    import glob
+    for tp in sorted(glob.glob(os.path.join(ROOT, "profiles", "*traffic.json"))):
+        tj = json.load(open(tp))
+        traffic, traffic_src = tj["dram_bytes_read"] + tj["dram_bytes_write"], os.path.basename(tp) + ": " + tj["capture"]
     roofline = {"kernel": "k_ptrace_closest", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": None, "peak_source": peak_src, "launches": tc["launches"], "avg_launch_ms": tc["ms"] / max(1, tc["launches"]),
+                "traffic": traffic, "traffic_source": traffic_src, "alg_bytes_per_launch": alg_bytes / max(1, tc["launches"]), "peak_source": peak_src, "launches": tc["launches"], "avg_launch_ms": tc["ms"] / max(1, tc["launches"]),
                 "node_tests_per_ray": tc["node_tests"] / max(1, path_rays), "prim_tests_per_ray": tc["prim_tests"] / max(1, path_rays),
                 "share_of_step": {k: (p["ms"] / total_ms if total_ms else 0) for k, p in prof.items()}}
 

@@ -41,7 +41,25 @@ RES = (1920, 1080)
 TOTAL_SPP = 1024
 
 
+WORKLOAD = "killeroo"
+
+
+def prepare_c4(quads):
+    """Config C4 (tools/gen_c4.py): generated on the box, once (local rank 0), the other ranks wait for it."""
+    d = os.path.join(tempfile.gettempdir(), "pbrtgpu_c4_%d" % quads)
+    done = os.path.join(d, "done")
+    if int(os.environ.get("LOCAL_RANK", "0")) == 0 and not os.path.exists(done):
+        subprocess.check_call([sys.executable, os.path.join(ROOT, "tools", "gen_c4.py"), d, "--quads", str(quads)], stdout=subprocess.DEVNULL)
+        open(done, "w").write("ok")
+    while not os.path.exists(done):
+        time.sleep(0.5)
+    return os.path.join(d, "c4.pbrt")
+
+
 def find_scene():
+    if WORKLOAD.startswith("c4"):
+        quads = int(WORKLOAD.split(":")[1]) if ":" in WORKLOAD else 2236
+        return prepare_c4(quads), "synthetic C4 scene (tools/gen_c4.py, %d triangles, 4 portal skylights, strategy portal)" % (2 * quads * quads)
     p = os.path.join(ROOT, "oracle", "_ref", "scenes", "killeroo-path.pbrt")
     if os.path.exists(p):
         return p, "killeroo-simple.pbrt (reference scene file, Integrator line set to \"path\")"
@@ -143,7 +161,7 @@ def reference_arm(args):
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": tot_s / args.steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
-        "data": "reference scene file", "config": {"workload": scene_desc + ", 1920x1080 path integrator maxdepth 5, halton", "sample": sample},
+        "data": "reference scene file", "config": {"workload": scene_desc + ", %dx%d path integrator maxdepth 5, halton" % RES, "sample": sample},
         "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
 
@@ -156,7 +174,13 @@ def main():
     ap.add_argument("--impl", default="ours")
     ap.add_argument("--spp-per-step", type=int, default=16)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="killeroo", help="killeroo (BASELINE.json configs[1], the default) | c4[:quads] (configs[3])")
     args = ap.parse_args()
+    global WORKLOAD, RES, TOTAL_SPP, METRIC
+    WORKLOAD = args.workload
+    if WORKLOAD.startswith("c4"):
+        RES, TOTAL_SPP = (3840, 2160), 4096
+        METRIC = "path samples per second (PathIntegrator::Li evaluations), synthetic 10M-triangle portal scene 3840x2160"
     if args.impl == "reference":
         return reference_arm(args)
 
@@ -274,7 +298,7 @@ def main():
     achieved = alg_bytes / (tc["ms"] / 1e3) / 1e9 if tc["ms"] > 0 else 0.0
     traffic, traffic_src = None, None
     import glob
-    for tp in sorted(glob.glob(os.path.join(ROOT, "profiles", "*traffic.json"))):
+    for tp in sorted(glob.glob(os.path.join(ROOT, "profiles", "*traffic.json"))) if WORKLOAD == "killeroo" else []:
         tj = json.load(open(tp))
         traffic, traffic_src = tj["dram_bytes_read"] + tj["dram_bytes_write"], os.path.basename(tp) + ": " + tj["capture"]
     roofline = {"kernel": "k_ptrace_closest", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
@@ -285,8 +309,8 @@ def main():
     out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
            "data": "reference scene file" if "reference scene" in scene_desc else "synthetic",
-           "config": {"workload": scene_desc + ", 1920x1080, Integrator path maxdepth 5, halton; one step = %d spp of the full frame per GPU "
-                      "(sample numbers of the 1024-spp job), 16x16 tiles sharded over ranks, film reduce per step" % S,
+           "config": {"workload": scene_desc + ", %dx%d" % RES + ", Integrator path maxdepth 5, halton; one step = %d spp of the full frame per GPU "
+                      "(sample numbers of the %d-spp job), 16x16 tiles sharded over ranks, film reduce per step" % (S, TOTAL_SPP),
                       "spp_per_step_per_gpu": S, "l2": "wavefront state of a step (%.0f MB) and the film exceed L2; no flush needed" %
                       (min(samples_per_step // world, 4 << 20) * 270 / 1e6), "rays_per_sample": float(tot[1].item()) / (samples_per_step * args.steps)},
            "gpu_launches": int(tot[0].item()), "clocks": clk,

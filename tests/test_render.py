@@ -223,3 +223,41 @@ def test_gpu_portal_estimator_variance_matches_reference(pkg, gpu, golden):
         assert ours <= ref * (1 + 1e-3), (strategy, ours, ref)
     # restricting the samples to the portal must pay off in this scene (the emitter is 16 x the hole)
     assert mse["portal"][0] < mse["light"][0], mse
+
+
+# ---------------------------------------------------------------- analytic known answers
+# The reference's only end-to-end known-answer test: src/tests/analytic_scenes.cpp:68-204 +
+# 287-289 (PathIntegrator, depth 8, 10 x 10 film, box filter 0.5, Halton 256): a camera inside a
+# unit sphere with Kd = 0.5 must see radiance 1.0 +- 0.02 in every channel on average.
+ANALYTIC_HEAD = ('Camera "perspective" "float fov" [45]\n'
+                 'Film "image" "integer xresolution" [10] "integer yresolution" [10] "string filename" "analytic.pfm"\n'
+                 'PixelFilter "box" "float xwidth" [0.5] "float ywidth" [0.5]\n'
+                 'Sampler "halton" "integer pixelsamples" [256]\nIntegrator "path" "integer maxdepth" [8]\nWorldBegin\n')
+ANALYTIC = {
+    "sphere_1_point_light": 'LightSource "point" "rgb I" [3.14159265 3.14159265 3.14159265]\n'
+                            'Material "matte" "rgb Kd" [.5 .5 .5] "float sigma" [0]\nReverseOrientation\nShape "sphere" "float radius" [1]\n',
+    "sphere_4_point_lights": 'LightSource "point" "rgb I" [0.785398163 0.785398163 0.785398163]\n' * 4 +
+                             'Material "matte" "rgb Kd" [.5 .5 .5] "float sigma" [0]\nReverseOrientation\nShape "sphere" "float radius" [1]\n',
+    "emissive_sphere": 'Material "matte" "rgb Kd" [.5 .5 .5] "float sigma" [0]\nReverseOrientation\n'
+                       'AreaLightSource "diffuse" "rgb L" [.5 .5 .5]\nShape "sphere" "float radius" [1]\n',
+}
+
+
+def analytic_scene(pkg, name):
+    return pkg.HostScene(text=ANALYTIC_HEAD + ANALYTIC[name] + "WorldEnd\n", base_dir=os.path.join(ROOT, "tests", "scenes"))
+
+
+@pytest.mark.parametrize("name", sorted(ANALYTIC))
+def test_analytic_scene_radiance_cpu_stepped(pkg, hostsim_lib, name):
+    rgb, _, _ = util.hostsim_render(hostsim_lib, analytic_scene(pkg, name))
+    assert abs(float(rgb.mean()) - 1.0) <= 0.02, float(rgb.mean())
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", sorted(ANALYTIC))
+def test_gpu_analytic_scene_radiance(pkg, gpu, name):
+    hs = analytic_scene(pkg, name)
+    gpu.upload(hs)
+    film, _ = gpu.render(hs.params)
+    mean = float(hs.film_to_rgb(film).mean())
+    assert abs(mean - 1.0) <= 0.02, mean

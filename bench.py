@@ -291,19 +291,27 @@ def main():
     ctx.set_profile(False)
     tc = prof["trace_closest"]
     total_ms = sum(p["ms"] for p in prof.values())
-    # algorithmic bytes of k_trace_closest: 32 B ray in + 16 B hit out per ray,
-    # 32 B per node test (sizeof LinearBVHNode), 48 B per primitive test (indices + vertices)
+    # The dominant kernel is the traversal launch (k_ptrace_closest for the camera rays, then one
+    # k_ptrace_fused per depth: path rays + next-event rays + shadow rays).  Algorithmic bytes
+    # (SURVEY.md 8(d)): 32 B ray in + 16 B hit out per closest-hit ray, 32 B in + 1 B out per any-hit
+    # ray, 32 B per node test (sizeof LinearBVHNode), 48 B per primitive test (indices + vertices).
     path_rays = pst.closest_rays - pst.nee_closest_rays
-    alg_bytes = 48.0 * path_rays + 32.0 * tc["node_tests"] + 48.0 * tc["prim_tests"]
+    node_tests = sum(prof[k]["node_tests"] for k in ("trace_closest", "trace_shadow", "trace_nee"))
+    prim_tests = sum(prof[k]["prim_tests"] for k in ("trace_closest", "trace_shadow", "trace_nee"))
+    alg_bytes = 48.0 * pst.closest_rays + 33.0 * pst.shadow_rays + 32.0 * node_tests + 48.0 * prim_tests
+    all_rays = pst.closest_rays + pst.shadow_rays
     achieved = alg_bytes / (tc["ms"] / 1e3) / 1e9 if tc["ms"] > 0 else 0.0
     traffic, traffic_src = None, None
     import glob
     for tp in sorted(glob.glob(os.path.join(ROOT, "profiles", "*traffic.json"))) if WORKLOAD == "killeroo" else []:
         tj = json.load(open(tp))
         traffic, traffic_src = tj["dram_bytes_read"] + tj["dram_bytes_write"], os.path.basename(tp) + ": " + tj["capture"]
-    roofline = {"kernel": "k_ptrace_closest", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+    roofline = {"kernel": "k_ptrace_fused (+ k_ptrace_closest for the camera rays)", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": traffic, "traffic_source": traffic_src, "alg_bytes_per_launch": alg_bytes / max(1, tc["launches"]), "peak_source": peak_src, "launches": tc["launches"], "avg_launch_ms": tc["ms"] / max(1, tc["launches"]),
-                "node_tests_per_ray": tc["node_tests"] / max(1, path_rays), "prim_tests_per_ray": tc["prim_tests"] / max(1, path_rays),
+                "node_tests_per_ray": node_tests / max(1, all_rays), "prim_tests_per_ray": prim_tests / max(1, all_rays),
+                "rays_in_profile_step": {"path_closest": int(path_rays), "nee_closest": int(pst.nee_closest_rays), "shadow_any": int(pst.shadow_rays),
+                                         "camera": int(pst.camera_rays)},
+                "kernel_ms_in_profile_step": {k: p["ms"] for k, p in prof.items()},
                 "share_of_step": {k: (p["ms"] / total_ms if total_ms else 0) for k, p in prof.items()}}
 
     out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,

@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define PBRTGPU_ABI_VERSION 1
+#define PBRTGPU_ABI_VERSION 2
 
 typedef enum {
     PBRTGPU_OK = 0,
@@ -158,6 +158,8 @@ typedef struct {
     int64_t kernel_launches;
     int64_t nee_closest_rays; /* the part of closest_rays traced for direct lighting (BSDF-sampled MIS rays, portal rays) */
     float device_ms;        /* CUDA-event time of the render, device only */
+    int64_t nee_rays_culled; /* BSDF-sampled MIS rays the reference would trace but which miss the sampled light's own shape:
+                                their closest hit cannot be that light, they contribute nothing and are not traced (not in closest_rays) */
 } pbrtgpu_stats;
 
 /* Kernels of the wavefront, for per-kernel timing (pbrtgpu_profile). */

@@ -69,7 +69,8 @@ def build_gpu(verbose=False):
     target = os.path.join(OUT, "libpbrtgpu.so")
     if srcs and _newer(target, srcs + _deps()):
         nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
-        log = _run([nvcc] + NVCC_FLAGS + ["-Xptxas", "-v", "-shared", "-I" + os.path.join(ROOT, "include")] + srcs +
+        extra = os.environ.get("PBRTGPU_EXTRA_NVCC_FLAGS", "").split()  # tuning experiments, e.g. -DPG_PERSIST_MIN_BLOCKS=8
+        log = _run([nvcc] + NVCC_FLAGS + extra + ["-Xptxas", "-v", "-shared", "-I" + os.path.join(ROOT, "include")] + srcs +
                    ["-o", target, "-lcudart"])
         with open(os.path.join(OUT, "ptxas.log"), "w") as f:
             f.write(log)

@@ -89,6 +89,27 @@ PG_HD bool slabPartial(V3 bmin, V3 bmax, V3 o, V3 invDir, const int dirIsNeg[3],
     return tMax > 0;
 }
 
+// One primitive against one ray, with the leaf loop's closest-hit acceptance.  Used to discard
+// next-event rays that cannot contribute: a BSDF-sampled MIS ray counts only if its CLOSEST hit is
+// the sampled light's own shape (integrator.cpp:226-233), and whatever the traversal has found
+// before it reaches that shape only shrinks ray.tMax, which never turns a rejection into an
+// acceptance (triangle.cpp:262-266, sphere.cpp:83-89, plane.cpp:27-29).  So "this test fails
+// with the ray's initial tMax" implies "the closest hit is not this shape".
+PG_HD bool primitiveAccepts(const DevBVH &bvh, int slot, const Ray &ray) {
+    const F4 *tp = bvh.tris + 3 * (size_t)slot;
+    F4 a = PG_LDG(tp);
+    int tag = f2i(a.w);
+    int type = tag & kTagTypeMask;
+    float t, b0, b1;
+    if (type == 0) {
+        if (tag & kTagDegenerate) return false;
+        F4 b = PG_LDG(tp + 1), c = PG_LDG(tp + 2);
+        return triangleTest(ray, v3(a.x, a.y, a.z), v3(b.x, b.y, b.z), v3(c.x, c.y, c.z), &t, &b0, &b1);
+    }
+    if (type == 1) return aaplaneTest(ray, bvh.planeParams + 48 * (size_t)(tag >> kTagShapeShift), &t, nullptr);
+    return sphereTest(ray, bvh.sphereParams + 48 * (size_t)(tag >> kTagShapeShift), &t, nullptr, nullptr, nullptr);
+}
+
 // Closest hit (ANY = false): ray.tMax shrinks as in GeometricPrimitive::
 // Intersect (primitive.cpp:116-130), the last accepted primitive wins.
 // Any hit (ANY = true): returns at the first accepted primitive.

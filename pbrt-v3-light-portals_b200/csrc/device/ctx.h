@@ -57,6 +57,7 @@ struct pbrtgpu_ctx {
     int smCount = 148;
     // trace kernel variant (tuning knobs, env PBRTGPU_TRACE_PERSISTENT / _FETCH_THRESHOLD / _PERSIST_BLOCKS)
     bool tracePersistent = true;
+    bool traceFused = true;   // one traversal launch per depth for path + next-event + shadow rays
     bool shadeSync = true;
     int shadeBlock = 768;
     int fetchThreshold = 8;

@@ -22,6 +22,7 @@ struct WaveCounters {
     int nHit[kMaxDepthSlots];         // of the nActive[d] rays: how many hit something (queue hitIdx) ...
     int nMiss[kMaxDepthSlots];        // ... and how many escaped (queue missIdx)
     int fetch[3][kMaxDepthSlots];     // persistent trace kernels: next unclaimed queue position {closest, shadow, nee}
+    int nNeeCulled[kMaxDepthSlots];   // MIS rays not traced because they miss the sampled light's shape (bvh.h:primitiveAccepts)
     unsigned long long cameraRays, closestRays, shadowRays, scrubbed;
 };
 

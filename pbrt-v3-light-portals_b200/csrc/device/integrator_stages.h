@@ -171,9 +171,17 @@ PG_HD void stageShadePhased(const WaveParams &w, int depth, int cur, int pos, bo
             if (lightPdf == 0) misRay = false;
             else weight = powerHeuristic(scatteringPdf, lightPdf);
         }
+        Ray nr;
+        if (misRay) {
+            nr = spawnRay(it.p, it.pError, it.n, wi);
+            // the ray can only count if its closest hit is the light's own shape: skip it when it misses that shape
+            if (lightTag == PBRTGPU_LIGHT_DIFFUSE_AREA && !primitiveAccepts(w.sc.bvh, PG_LD(w.sc.lightPrim + li), nr)) {
+                misRay = false;
+                atomicIncInt(&w.cnt->nNeeCulled[depth]);
+            }
+        }
         if (misRay) {
             Spec c = beta * ((fMis * weight / scatteringPdf) / pickPdf);
-            Ray nr = spawnRay(it.p, it.pError, it.n, wi);
             int np = atomicIncInt(&w.cnt->nNee[depth]);
             storeRay(w.neeRays, np, nr);
             w.neeContrib[np] = f4(c.r, c.g, c.b, bitsToFloat((unsigned)slot));

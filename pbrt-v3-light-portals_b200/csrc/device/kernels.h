@@ -11,7 +11,7 @@ namespace pg {
 constexpr int kTraceBlock = 128;
 constexpr int kTraceBlocksPerSM = 8;
 #ifndef PG_PERSIST_MIN_BLOCKS
-#define PG_PERSIST_MIN_BLOCKS 6
+#define PG_PERSIST_MIN_BLOCKS 8
 #endif
 constexpr int kPersistMinBlocks = PG_PERSIST_MIN_BLOCKS;  // persistent trace kernels: resident blocks per SM the register budget allows
 

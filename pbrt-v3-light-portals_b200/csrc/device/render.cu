@@ -69,28 +69,76 @@ __global__ void __launch_bounds__(kTraceBlock) k_trace_closest(WaveParams w, int
 template <bool COUNT>
 __global__ void __launch_bounds__(kTraceBlock, kPersistMinBlocks) k_ptrace_closest(WaveParams w, int depth, int cur) {
     TraverseCounters c = {0, 0};
-    tracePersistent<false, COUNT>(w.sc.bvh, w.rays[cur], w.cnt->nActive[depth], &w.cnt->fetch[0][depth], w.fetchThreshold, w.phaseBias, &c,
-                                  [&](int i, const Ray &, const Hit &h, bool) {
-                                      w.hits[i] = f4(__int_as_float(h.prim), h.b0, h.b1, h.b2);
-                                  });
+    tracePersistent<kTraceClosest, COUNT>(w.sc.bvh, SingleQueue{w.rays[cur], 0}, w.cnt->nActive[depth], &w.cnt->fetch[0][depth],
+                                          w.fetchThreshold, w.phaseBias, &c, [&](int i, int, const Ray &, const Hit &h, bool) {
+                                              w.hits[i] = f4(__int_as_float(h.prim), h.b0, h.b1, h.b2);
+                                          });
     flushCounts<COUNT>(w, 0, c);
 }
 
+// Everything shade(depth) asked for, in ONE launch: the path rays of depth + 1 (closest hit), the
+// BSDF-sampled / portal next-event rays of this depth (closest hit) and its light-sample rays (any
+// hit) form one queue, heaviest kind first.  One launch has one tail (the last rays in flight keep
+// few lanes busy) instead of three, and the short any-hit rays fill the lanes the long ones vacate.
+struct FusedQueue {
+    const F4 *path, *nee, *shadow;
+    int nPath, nNee;
+    __device__ __forceinline__ int operator()(int idx, Ray *ray) const {
+        if (idx < nPath) {
+            *ray = loadRayF4(path, idx);
+            return 0;
+        }
+        idx -= nPath;
+        if (idx < nNee) {
+            *ray = loadRayF4(nee, idx);
+            return 2;
+        }
+        *ray = loadRayF4(shadow, idx - nNee);
+        return 1;
+    }
+};
+
+template <bool COUNT>
+__global__ void __launch_bounds__(kTraceBlock, kPersistMinBlocks) k_ptrace_fused(WaveParams w, int depth, int cur) {
+    TraverseCounters c[3] = {{0, 0}, {0, 0}, {0, 0}};
+    const int nPath = w.cnt->nActive[depth + 1], nNee = w.cnt->nNee[depth], nShadow = w.cnt->nShadow[depth];
+    FusedQueue q = {w.rays[cur ^ 1], w.neeRays, w.shadowRays, nPath, nNee};
+    tracePersistent<kTraceMixed, COUNT>(w.sc.bvh, q, nPath + nNee + nShadow, &w.cnt->fetch[1][depth], w.fetchThreshold, w.phaseBias, c,
+                                        [&](int i, int kind, const Ray &, const Hit &h, bool found) {
+                                            if (kind == 0) w.hits[i] = f4(__int_as_float(h.prim), h.b0, h.b1, h.b2);
+                                            else if (kind == 2) w.neeHits[i - nPath] = f4(__int_as_float(h.prim), h.b0, h.b1, h.b2);
+                                            else w.shadowOcc[i - nPath - nNee] = found ? 1 : 0;
+                                        });
+    flushCounts<COUNT>(w, 0, c[0]);
+    flushCounts<COUNT>(w, 1, c[1]);
+    flushCounts<COUNT>(w, 2, c[2]);
+}
+
 // hit / miss positions of the depth-d queue, in queue order (so that k_shade reads its inputs nearly in order)
+__device__ __forceinline__ void splitHits(const WaveParams &w, int depth, bool wantMiss, int i) {
+    if (__float_as_int(w.hits[i].x) >= 0) w.hitIdx[atomicIncInt(&w.cnt->nHit[depth])] = i;
+    else if (wantMiss) w.missIdx[atomicIncInt(&w.cnt->nMiss[depth])] = i;
+}
 __global__ void __launch_bounds__(kStageBlock) k_split_hits(WaveParams w, int depth, bool wantMiss) {
     int n = w.cnt->nActive[depth];
     int stride = gridDim.x * blockDim.x;
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        if (__float_as_int(w.hits[i].x) >= 0) w.hitIdx[atomicIncInt(&w.cnt->nHit[depth])] = i;
-        else if (wantMiss) w.missIdx[atomicIncInt(&w.cnt->nMiss[depth])] = i;
-    }
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) splitHits(w, depth, wantMiss, i);
+}
+
+// after k_ptrace_fused(depth): the light samples of this depth count where unoccluded, and the
+// next depth's queue is split into hits and misses
+__global__ void __launch_bounds__(kStageBlock) k_post_trace(WaveParams w, int depth, bool wantMiss) {
+    int nS = w.cnt->nShadow[depth], nA = w.cnt->nActive[depth + 1];
+    int stride = gridDim.x * blockDim.x;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < nS; i += stride) stageShadowResolve(w, i, w.shadowOcc[i] != 0);
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < nA; i += stride) splitHits(w, depth + 1, wantMiss, i);
 }
 
 template <bool COUNT>
 __global__ void __launch_bounds__(kTraceBlock, kPersistMinBlocks) k_ptrace_shadow(WaveParams w, int depth) {
     TraverseCounters c = {0, 0};
-    tracePersistent<true, COUNT>(w.sc.bvh, w.shadowRays, w.cnt->nShadow[depth], &w.cnt->fetch[1][depth], w.fetchThreshold, w.phaseBias, &c,
-                                 [&](int i, const Ray &, const Hit &, bool occluded) { w.shadowOcc[i] = occluded ? 1 : 0; });
+    tracePersistent<kTraceAny, COUNT>(w.sc.bvh, SingleQueue{w.shadowRays, 1}, w.cnt->nShadow[depth], &w.cnt->fetch[1][depth], w.fetchThreshold,
+                                      w.phaseBias, &c, [&](int i, int, const Ray &, const Hit &, bool occluded) { w.shadowOcc[i] = occluded ? 1 : 0; });
     flushCounts<COUNT>(w, 1, c);
 }
 
@@ -103,10 +151,10 @@ __global__ void __launch_bounds__(kStageBlock) k_shadow_resolve(WaveParams w, in
 template <bool COUNT>
 __global__ void __launch_bounds__(kTraceBlock, kPersistMinBlocks) k_ptrace_nee(WaveParams w, int depth) {
     TraverseCounters c = {0, 0};
-    tracePersistent<false, COUNT>(w.sc.bvh, w.neeRays, w.cnt->nNee[depth], &w.cnt->fetch[2][depth], w.fetchThreshold, w.phaseBias, &c,
-                                  [&](int i, const Ray &, const Hit &h, bool) {
-                                      w.neeHits[i] = f4(__int_as_float(h.prim), h.b0, h.b1, h.b2);
-                                  });
+    tracePersistent<kTraceClosest, COUNT>(w.sc.bvh, SingleQueue{w.neeRays, 0}, w.cnt->nNee[depth], &w.cnt->fetch[2][depth], w.fetchThreshold,
+                                          w.phaseBias, &c, [&](int i, int, const Ray &, const Hit &h, bool) {
+                                              w.neeHits[i] = f4(__int_as_float(h.prim), h.b0, h.b1, h.b2);
+                                          });
     flushCounts<COUNT>(w, 2, c);
 }
 
@@ -182,9 +230,11 @@ __global__ void __launch_bounds__(kStageBlock) k_film(WaveParams w) {
 // fold one batch's counters into the running totals, then clear them for the next batch
 __global__ void k_batch_stats(WaveCounters *cnt, unsigned long long *totals, int depths) {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
-    unsigned long long closest = 0, shadow = 0, nee = 0;
+    unsigned long long closest = 0, shadow = 0, nee = 0, culled = 0;
     for (int d = 0; d <= depths; ++d) closest += (unsigned long long)cnt->nActive[d];
-    for (int d = 0; d < depths; ++d) nee += (unsigned long long)cnt->nNee[d], shadow += (unsigned long long)cnt->nShadow[d];
+    for (int d = 0; d < depths; ++d)
+        nee += (unsigned long long)cnt->nNee[d], shadow += (unsigned long long)cnt->nShadow[d], culled += (unsigned long long)cnt->nNeeCulled[d];
+    totals[5] += culled;
     totals[0] += (unsigned long long)cnt->nActive[0];
     totals[1] += closest + nee;
     totals[4] += nee;
@@ -192,7 +242,7 @@ __global__ void k_batch_stats(WaveCounters *cnt, unsigned long long *totals, int
     totals[3] += cnt->scrubbed;
     for (int d = 0; d <= kMaxDepthSlots; ++d) cnt->nActive[d] = 0;
     for (int d = 0; d < kMaxDepthSlots; ++d)
-        cnt->nShadow[d] = cnt->nNee[d] = cnt->nHit[d] = cnt->nMiss[d] = cnt->fetch[0][d] = cnt->fetch[1][d] = cnt->fetch[2][d] = 0;
+        cnt->nShadow[d] = cnt->nNee[d] = cnt->nHit[d] = cnt->nMiss[d] = cnt->fetch[0][d] = cnt->fetch[1][d] = cnt->fetch[2][d] = cnt->nNeeCulled[d] = 0;
     cnt->scrubbed = 0;
 }
 

@@ -48,7 +48,7 @@ __global__ void __launch_bounds__(kTraceBlock) k_intersect_any(DevScene sc, cons
 // Persistent variants (trace_persistent.h); `rays` / outputs already offset to the chunk, n < 2^31.
 __global__ void __launch_bounds__(kTraceBlock, kPersistMinBlocks) k_pintersect_closest(DevScene sc, const float4 *__restrict__ rays, int n,
                                                                     float4 *__restrict__ hits, int *next, int fetchThreshold, int phaseBias) {
-    tracePersistent<false, false>(sc.bvh, rays, n, next, fetchThreshold, phaseBias, nullptr, [&](int i, const Ray &ray, const Hit &h, bool found) {
+    tracePersistent<kTraceClosest, false>(sc.bvh, SingleQueue{rays, 0}, n, next, fetchThreshold, phaseBias, nullptr, [&](int i, int, const Ray &ray, const Hit &h, bool found) {
         float4 out;
         out.x = __int_as_float(found ? __ldg(sc.primOrigId + h.prim) : -1);
         out.y = ray.tMax;
@@ -60,8 +60,8 @@ __global__ void __launch_bounds__(kTraceBlock, kPersistMinBlocks) k_pintersect_c
 
 __global__ void __launch_bounds__(kTraceBlock, kPersistMinBlocks) k_pintersect_any(DevScene sc, const float4 *__restrict__ rays, int n,
                                                                 unsigned char *__restrict__ occluded, int *next, int fetchThreshold, int phaseBias) {
-    tracePersistent<true, false>(sc.bvh, rays, n, next, fetchThreshold, phaseBias, nullptr,
-                                 [&](int i, const Ray &, const Hit &, bool occ) { occluded[i] = occ ? 1 : 0; });
+    tracePersistent<kTraceAny, false>(sc.bvh, SingleQueue{rays, 1}, n, next, fetchThreshold, phaseBias, nullptr,
+                                      [&](int i, int, const Ray &, const Hit &, bool occ) { occluded[i] = occ ? 1 : 0; });
 }
 
 int traceGrid(const pbrtgpu_ctx *ctx, long long n) {

@@ -54,20 +54,36 @@ __device__ __forceinline__ bool slabPartialFlat(V3 bmin, V3 bmax, V3 o, V3 invDi
     return !missXY && !missZ && tMax > 0;
 }
 
-// sink(idx, ray, hit, found): called once per ray by the lane that finished it.
+// sink(idx, kind, ray, hit, found): called once per ray by the lane that finished it.
 // `next` is a device counter that is 0 at launch.  fetchThreshold: refill when
 // at least this many lanes of the warp are idle (1..32).  phaseBias (in 1/16):
 // a round runs box tests when 16 * (#lanes at an interior record) >=
 // phaseBias * (#lanes at a primitive), else one primitive test per such lane.
-template <bool ANY, bool COUNT, class Sink>
-__device__ __forceinline__ void tracePersistent(const DevBVH &bvh, const F4 *__restrict__ rays, int n, int *next,
-                                                int fetchThreshold, int phaseBias, TraverseCounters *cnt, Sink sink) {
+//
+// MODE: kTraceClosest / kTraceAny for a queue of one kind, kTraceMixed when the queue holds both kinds.
+// source(idx, &ray) loads ray `idx` and returns its kind (0 = closest hit, 1 = any hit; in mixed mode
+// any other small integer >= 2 is a closest-hit ray of another sub-queue); the kind indexes cnt[] and
+// is handed back to sink(idx, kind, ray, hit, found).
+enum { kTraceClosest = 0, kTraceAny = 1, kTraceMixed = 2 };
+
+struct SingleQueue {  // one ray array, one kind
+    const F4 *rays;
+    int kind;
+    __device__ __forceinline__ int operator()(int idx, Ray *ray) const {
+        *ray = loadRayF4(rays, idx);
+        return kind;
+    }
+};
+
+template <int MODE, bool COUNT, class Source, class Sink>
+__device__ __forceinline__ void tracePersistent(const DevBVH &bvh, Source source, int n, int *next, int fetchThreshold,
+                                                int phaseBias, TraverseCounters *cnt, Sink sink) {
     const unsigned kFull = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     int stackRef[64];
     float stackT[64];
     // ref >= 0: interior record to visit; ref < 0: ~ref is the next primitive slot to test; kEmptyRef: no ray
-    int sp = 0, ref = kEmptyRef, idx = -1;
+    int sp = 0, ref = kEmptyRef, idx = -1, kind = MODE == kTraceAny ? 1 : 0;
     Ray ray;
     ray.o = ray.d = v3(0.f);
     ray.tMax = 0;
@@ -80,6 +96,13 @@ __device__ __forceinline__ void tracePersistent(const DevBVH &bvh, const F4 *__r
     hit.prim = -1;
     hit.t = hit.b0 = hit.b1 = hit.b2 = 0;
     bool exhausted = false;  // warp-uniform: the queue has been handed out completely
+    // The first 32 rays of every warp are assigned statically (queue positions [32 * warp, 32 * warp + 32));
+    // the shared cursor `next` hands out what lies beyond all warps' first chunks.  A launch over a short
+    // queue therefore costs no atomics at all.
+    const int warpsInGrid = (gridDim.x * blockDim.x) >> 5;
+    const int warpId = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int dynamicBegin = warpsInGrid * 32;
+    bool first = true;
 
     for (;;) {
         unsigned idle = __ballot_sync(kFull, ref == kEmptyRef);
@@ -88,13 +111,19 @@ __device__ __forceinline__ void tracePersistent(const DevBVH &bvh, const F4 *__r
             if (!exhausted && nIdle >= fetchThreshold) {
                 int leader = __ffs(idle) - 1;
                 int base = 0;
-                if (lane == leader) base = atomicAdd(next, nIdle);
-                base = __shfl_sync(kFull, base, leader);
+                if (first) {
+                    base = warpId * 32;
+                    first = false;
+                    if (dynamicBegin >= n) exhausted = true;  // nothing for the cursor to hand out
+                } else {
+                    if (lane == leader) base = dynamicBegin + atomicAdd(next, nIdle);
+                    base = __shfl_sync(kFull, base, leader);
+                }
                 if (ref == kEmptyRef) {
                     int mine = base + __popc(idle & ((1u << lane) - 1));
                     if (mine < n) {
                         idx = mine;
-                        ray = loadRayF4(rays, idx);
+                        kind = source(idx, &ray);
                         invDir = v3(1 / ray.d.x, 1 / ray.d.y, 1 / ray.d.z);
                         dirIsNeg[0] = invDir.x < 0, dirIsNeg[1] = invDir.y < 0, dirIsNeg[2] = invDir.z < 0;
                         shear = rayShear(ray.d);
@@ -103,10 +132,11 @@ __device__ __forceinline__ void tracePersistent(const DevBVH &bvh, const F4 *__r
                         ref = 0;
                     }
                 }
-                exhausted = base + nIdle >= n;
+                exhausted = exhausted || (base >= dynamicBegin && base + nIdle >= n);
             }
             if (exhausted && __all_sync(kFull, ref == kEmptyRef)) return;
         }
+        const bool any = MODE == kTraceMixed ? kind == 1 : MODE == kTraceAny;
         const bool atInterior = ref >= 0, atPrim = ref < 0 && ref != kEmptyRef;
         int nI = __popc(__ballot_sync(kFull, atInterior)), nP = __popc(__ballot_sync(kFull, atPrim));
         bool popNext = false, occluded = false;
@@ -115,7 +145,7 @@ __device__ __forceinline__ void tracePersistent(const DevBVH &bvh, const F4 *__r
             if (atInterior) {
                 const F4 *nd = bvh.nodes + 4 * (size_t)ref;
                 F4 q0 = __ldg(nd), q1 = __ldg(nd + 1), q2 = __ldg(nd + 2), q3 = __ldg(nd + 3);
-                if (COUNT) cnt->nodes += 2;
+                if (COUNT) cnt[MODE == kTraceMixed ? kind : 0].nodes += 2;
                 int ref0 = f2i(q3.x), ref1 = f2i(q3.y), axis = f2i(q3.z);
                 float t0, t1;
                 bool ok0 = ref0 != kEmptyRef && slabPartialFlat(v3(q0.x, q0.y, q0.z), v3(q0.w, q1.x, q1.y), ray.o, invDir, dirIsNeg, &t0);
@@ -143,20 +173,20 @@ __device__ __forceinline__ void tracePersistent(const DevBVH &bvh, const F4 *__r
             F4 a = __ldg(tp);
             int tag = f2i(a.w);
             int type = tag & kTagTypeMask;
-            if (COUNT) cnt->prims += 1;
+            if (COUNT) cnt[MODE == kTraceMixed ? kind : 0].prims += 1;
             float t, b0 = 0, b1 = 0, b2 = 0;
             bool h;
             if (type == 0) {
                 F4 b = __ldg(tp + 1), c = __ldg(tp + 2);
                 h = triangleTestSheared(ray, shear, v3(a.x, a.y, a.z), v3(b.x, b.y, b.z), v3(c.x, c.y, c.z), &t, &b0, &b1, &b2);
-                if (!ANY && (tag & kTagDegenerate)) h = false;
+                if (!any && (tag & kTagDegenerate)) h = false;
             } else if (type == 1) {
                 h = aaplaneTest(ray, bvh.planeParams + 48 * (size_t)(tag >> kTagShapeShift), &t, nullptr);
             } else {
                 h = sphereTest(ray, bvh.sphereParams + 48 * (size_t)(tag >> kTagShapeShift), &t, nullptr, nullptr, nullptr);
             }
             if (h) {
-                if (ANY) occluded = true;
+                if (any) occluded = true;
                 else {
                     ray.tMax = t;
                     hit.prim = slot;
@@ -186,7 +216,7 @@ __device__ __forceinline__ void tracePersistent(const DevBVH &bvh, const F4 *__r
                 }
             }
         }
-        if ((atInterior || atPrim) && ref == kEmptyRef) sink(idx, ray, hit, ANY ? occluded : hit.prim >= 0);
+        if ((atInterior || atPrim) && ref == kEmptyRef) sink(idx, kind, ray, hit, any ? occluded : hit.prim >= 0);
     }
 }
 

@@ -71,6 +71,7 @@ int pbrtgpu_create(int cuda_device, pbrtgpu_ctx **out) {
     ctx->ownStream = true;
     cudaDeviceGetAttribute(&ctx->smCount, cudaDevAttrMultiProcessorCount, cuda_device);
     if (const char *v = getenv("PBRTGPU_TRACE_PERSISTENT")) ctx->tracePersistent = atoi(v) != 0;
+    if (const char *v = getenv("PBRTGPU_TRACE_FUSED")) ctx->traceFused = atoi(v) != 0;
     if (const char *v = getenv("PBRTGPU_SHADE_SYNC")) ctx->shadeSync = atoi(v) != 0;
     if (const char *v = getenv("PBRTGPU_FETCH_THRESHOLD")) ctx->fetchThreshold = std::min(32, std::max(1, atoi(v)));
     if (const char *v = getenv("PBRTGPU_SHADE_BLOCK")) ctx->shadeBlock = atoi(v);
@@ -88,7 +89,7 @@ int pbrtgpu_create(int cuda_device, pbrtgpu_ctx **out) {
         for (size_t i = 0; i < primes.size(); ++i) sums[i] = acc, acc += primes[i];
         if ((e = cudaMalloc((void **)&ctx->dPrimes, primes.size() * sizeof(int))) != cudaSuccess) return bail(e, "cudaMalloc(primes)");
         if ((e = cudaMalloc((void **)&ctx->dPrimeSums, primes.size() * sizeof(int))) != cudaSuccess) return bail(e, "cudaMalloc(primeSums)");
-        if ((e = cudaMalloc((void **)&ctx->dTotals, 5 * sizeof(unsigned long long))) != cudaSuccess) return bail(e, "cudaMalloc(totals)");
+        if ((e = cudaMalloc((void **)&ctx->dTotals, 6 * sizeof(unsigned long long))) != cudaSuccess) return bail(e, "cudaMalloc(totals)");
         cudaMemcpy(ctx->dPrimes, primes.data(), primes.size() * sizeof(int), cudaMemcpyHostToDevice);
         cudaMemcpy(ctx->dPrimeSums, sums.data(), primes.size() * sizeof(int), cudaMemcpyHostToDevice);
         std::vector<unsigned long long> magic = primeMagics(primes);

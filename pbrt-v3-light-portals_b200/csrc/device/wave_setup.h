@@ -65,7 +65,7 @@ inline BatchPlan planBatches(const pbrtgpu_render_params *rp, long long targetSl
     // material-less primitives do not count as bounces (path.cpp:108-113), so
     // leave room for a few of those when the scene has any
     p.depthIters = rp->max_depth + 1 + (hasNullMaterial ? 8 : 0);
-    if (p.depthIters > kMaxDepthSlots) p.depthIters = kMaxDepthSlots;
+    if (p.depthIters > kMaxDepthSlots - 1) p.depthIters = kMaxDepthSlots - 1;  // stage d touches the counters of depth d + 1
     return p;
 }
 

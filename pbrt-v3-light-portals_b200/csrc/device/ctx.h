@@ -59,7 +59,7 @@ struct pbrtgpu_ctx {
     bool tracePersistent = true;
     bool traceFused = true;   // one traversal launch per depth for path + next-event + shadow rays
     bool shadeSync = true;
-    int shadeBlock = 768;
+    int shadeBlock = 1024;
     int fetchThreshold = 8;
     int phaseBias = 16;
     int persistBlocksPerSM = pg::kPersistMinBlocks;

@@ -120,6 +120,8 @@ typedef struct {
 
     float world_center[3]; /* Scene::WorldBound().BoundingSphere, for infinite/distant lights (infinite.cpp:68-70) */
     float world_radius;
+    const int32_t *light_nsamples; /* Light::nSamples ("samples" / "nsamples", diffuse.cpp:110-111, infinite.cpp:158; 1 for delta lights):
+                                      read by Integrator "directlighting" strategy "all" only; NULL = 1 each */
 } pbrtgpu_scene;
 
 typedef struct {
@@ -148,7 +150,14 @@ typedef struct {
     int32_t shard_index, shard_count;
     /* sample range [spp_begin, spp_end) of every pixel; 0,0 = all spp */
     int32_t spp_begin, spp_end;
+    /* which SamplerIntegrator::Li: PBRTGPU_INTEGRATOR_PATH (path.cpp:64-189), or
+     * PBRTGPU_INTEGRATOR_DIRECT (directlighting.cpp:63-98: direct light at each vertex + specular
+     * reflection; max_depth is its "maxdepth", rr_threshold / light_strategy are unused) */
+    int32_t integrator;
+    int32_t direct_strategy; /* PBRTGPU_DIRECT_ALL (UniformSampleAllLights, integrator.cpp:69-98) or PBRTGPU_DIRECT_ONE */
 } pbrtgpu_render_params;
+enum { PBRTGPU_INTEGRATOR_PATH = 0, PBRTGPU_INTEGRATOR_DIRECT = 1 };
+enum { PBRTGPU_DIRECT_ALL = 0, PBRTGPU_DIRECT_ONE = 1 };
 
 typedef struct {
     int64_t camera_rays;    /* "Integrator/Camera rays traced" (integrator.cpp:52) */

@@ -44,7 +44,7 @@ class SceneView(C.Structure):  # pbrtgpu_scene
         ("n_lights", C.c_int32), ("light_tag", _p(C.c_int32)), ("light_prim", _p(C.c_int32)),
         ("light_strategy", _p(C.c_int32)), ("light_portal_begin", _p(C.c_int32)), ("light_params", _p(C.c_float)),
         ("n_portals", C.c_int32), ("portal_params", _p(C.c_float)),
-        ("world_center", C.c_float * 3), ("world_radius", C.c_float),
+        ("world_center", C.c_float * 3), ("world_radius", C.c_float), ("light_nsamples", _p(C.c_int32)),
     ]
 
     def array(self, name, count, width=1):
@@ -68,6 +68,7 @@ class RenderParams(C.Structure):  # pbrtgpu_render_params
         ("max_depth", C.c_int32), ("rr_threshold", C.c_float), ("light_strategy", C.c_int32),
         ("shard_index", C.c_int32), ("shard_count", C.c_int32),
         ("spp_begin", C.c_int32), ("spp_end", C.c_int32),
+        ("integrator", C.c_int32), ("direct_strategy", C.c_int32),
     ]
 
     def copy(self):

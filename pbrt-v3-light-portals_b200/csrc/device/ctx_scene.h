@@ -23,6 +23,7 @@ struct DevScene {
     const int *lightPrim;
     const int *lightStrategy;
     const int *lightPortalBegin;
+    const int *lightNSamples;  // Light::nSamples, or null = 1 each (directlighting "all" only)
     const float *lightParams;
     const float *portalParams;
     const float *lightCdf;  // nLights+1 (power strategy) or null

@@ -148,27 +148,20 @@ PG_HD_NOINLINE void estimateDirectPortal(const DevScene &sc, int li, const SurfI
     out->light = li;
 }
 
-// UniformSampleOneLight + EstimateDirect, up to the rays.  `scale` = beta;
-// the pick probability is folded in here.
-PG_HD void sampleOneLight(const DevScene &sc, const HaltonParams &hal, PathSampler &smp, const SurfInt &it, const BSDF &bsdf,
-                          Spec beta, NeeRequest *out) {
+// EstimateDirect for light `li` up to its rays (integrator.cpp:124-258; the portal hook :130-133),
+// in one piece.  The path integrator's shade stage has the same steps spread over its phases
+// (integrator_stages.h); this form serves Integrator "directlighting", which calls it once per
+// light sample.  `scale` multiplies both contributions (throughput / pick pdf or / nSamples).
+PG_HD_NOINLINE void estimateDirectRays(const DevScene &sc, int li, const SurfInt &it, const BSDF &bsdf, float uL0, float uL1, float uS0,
+                                       float uS1, Spec scale, NeeRequest *out, bool *culled) {
     out->hasShadow = out->hasClosest = false;
     out->light = -1;
     out->mode = NEE_MIS_LIGHT;
-    if (sc.nLights == 0) return;
-    float uPick = get1D(hal, smp);
-    int li = findIntervalCdf(sc.lightCdf, sc.nLights + 1, uPick);
-    float pickPdf = (sc.lightFuncInt > 0) ? PG_LD(sc.lightFunc + li) / (sc.lightFuncInt * sc.nLights) : 0;
-    if (pickPdf == 0) return;
-    float uL0, uL1, uS0, uS1;
-    get2D(hal, smp, &uL0, &uL1);
-    get2D(hal, smp, &uS0, &uS1);
+    *culled = false;
     int tag = PG_LD(sc.lightTag + li);
     if (tag == PBRTGPU_LIGHT_PORTAL_AREA) {
-        NeeRequest r = *out;
-        estimateDirectPortal(sc, li, it, bsdf, uS0, uS1, spec(1.f), &r);
-        if (r.hasClosest) r.closestContrib = beta * (r.closestContrib / pickPdf);
-        *out = r;
+        estimateDirectPortal(sc, li, it, bsdf, uS0, uS1, spec(1.f), out);
+        if (out->hasClosest) out->closestContrib = scale * out->closestContrib;
         return;
     }
     const int flagsNS = BSDF_ALL & ~BSDF_SPECULAR;
@@ -186,7 +179,7 @@ PG_HD void sampleOneLight(const DevScene &sc, const HaltonParams &hal, PathSampl
             else Ld = f * Li * powerHeuristic(lightPdf, scatteringPdf) / lightPdf;
             out->hasShadow = true;
             out->shadowRay = spawnRayTo(it.p, it.pError, it.n, pL.p, pL.pError, pL.n);
-            out->shadowContrib = beta * (Ld / pickPdf);
+            out->shadowContrib = scale * Ld;
         }
     }
     if (!isDelta) {
@@ -201,9 +194,15 @@ PG_HD void sampleOneLight(const DevScene &sc, const HaltonParams &hal, PathSampl
                 if (lightPdf == 0) return;
                 weight = powerHeuristic(scatteringPdf, lightPdf);
             }
+            Ray nr = spawnRay(it.p, it.pError, it.n, wi);
+            // the ray can only count if its closest hit is the light's own shape (bvh.h:primitiveAccepts)
+            if (tag == PBRTGPU_LIGHT_DIFFUSE_AREA && !primitiveAccepts(sc.bvh, PG_LD(sc.lightPrim + li), nr)) {
+                *culled = true;
+                return;
+            }
             out->hasClosest = true;
-            out->closestRay = spawnRay(it.p, it.pError, it.n, wi);
-            out->closestContrib = beta * ((f * weight / scatteringPdf) / pickPdf);
+            out->closestRay = nr;
+            out->closestContrib = scale * (f * weight / scatteringPdf);
             out->light = li;
             out->mode = NEE_MIS_LIGHT;
         }

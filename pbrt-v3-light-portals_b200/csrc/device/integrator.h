@@ -41,6 +41,9 @@ struct WaveParams {
     FilmParams film;
     int maxDepth;
     float rrThreshold;
+    int integrator, directStrategy;  // PBRTGPU_INTEGRATOR_*, PBRTGPU_DIRECT_*
+    int nSampleArrays;               // 2D sample arrays the integrator requested (DirectLightingIntegrator::Preprocess)
+    int neeCapacity;                 // entries of the shadow / next-event queues (nSlots x light samples per vertex)
     // batch geometry: slot -> (pixel, sample number)
     int tilesX;            // sample-bounds tiles per row (16 x 16 tiles as integrator.cpp:533-553)
     int shardIndex, shardCount;
@@ -52,7 +55,8 @@ struct WaveParams {
     int *dim;              // next sampler dimension
     F4 *L;                 // rgb = radiance so far, w = hero wavelength (nm)
     F4 *beta;              // rgb = throughput, w = etaScale
-    int *flags;            // bits 0-7 bounces, bit 8 specularBounce, bit 9 alive (has a film sample)
+    int *flags;            // bits 0-7 bounces, bit 8 specularBounce, bit 9 alive (has a film sample),
+                           // bits 10-25 vertices shaded so far (directlighting: which sample arrays are next)
     float *pFilm;          // 2 per slot
     // queues (position-indexed)
     F4 *rays[2];           // closest-hit rays of the current / next depth, 2 x float4 each

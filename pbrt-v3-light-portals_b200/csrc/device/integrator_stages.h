@@ -238,14 +238,151 @@ PG_HD void stageShadePhased(const WaveParams &w, int depth, int cur, int pos, bo
 
 PG_HD void stageShade(const WaveParams &w, int depth, int cur, int pos) { stageShadePhased(w, depth, cur, pos, true, NoSync()); }
 
+// ---- stage 3 for Integrator "directlighting": DirectLightingIntegrator::Li (directlighting.cpp:63-98)
+// at one vertex.  Direct light from all lights (UniformSampleAllLights, integrator.cpp:69-98, with the
+// sampler's 2D arrays) or from one (UniformSampleOneLight without a light distribution,
+// integrator.cpp:100-122), then SpecularReflect (integrator.cpp:639-675).  SpecularTransmit is not
+// followed: materials with specular transmission are refused at load (host/setup.cpp); for all other
+// materials its Sample_f finds no lobe and returns black, and the Get2D it draws comes after everything
+// this path still uses.  The recursion f * Li(...) * |cos| / pdf is carried as throughput.
+PG_HD void pushDirectRays(const WaveParams &w, int depth, int slot, const NeeRequest &r) {
+    if (r.hasShadow) {
+        int sp = atomicIncInt(&w.cnt->nShadow[depth]);
+        if (sp < w.neeCapacity) {
+            storeRay(w.shadowRays, sp, r.shadowRay);
+            w.shadowContrib[sp] = f4(r.shadowContrib.r, r.shadowContrib.g, r.shadowContrib.b, bitsToFloat((unsigned)slot));
+        }
+    }
+    if (r.hasClosest) {
+        int np = atomicIncInt(&w.cnt->nNee[depth]);
+        if (np < w.neeCapacity) {
+            storeRay(w.neeRays, np, r.closestRay);
+            w.neeContrib[np] = f4(r.closestContrib.r, r.closestContrib.g, r.closestContrib.b, bitsToFloat((unsigned)slot));
+            w.neeInfo[2 * (size_t)np] = r.light;
+            w.neeInfo[2 * (size_t)np + 1] = r.mode;
+        }
+    }
+}
+
+PG_HD void stageShadeDirect(const WaveParams &w, int depth, int cur, int pos) {
+    int slot = w.qSlot[cur][pos];
+    Ray ray = loadRay(w.rays[cur], pos);
+    F4 hit = w.hits[pos];
+    int prim = f2i(hit.x);
+    F4 Lq = w.L[slot], bq = w.beta[slot];
+    Spec L = spec(Lq.x, Lq.y, Lq.z), beta = spec(bq.x, bq.y, bq.z);
+    float wvl0 = Lq.w;
+    int flags = w.flags[slot];
+    int bounces = flags & 255, vertices = (flags >> 10) & 0xffff;
+    SurfInt it = hitInteraction(w.sc, prim, hit.y, hit.z, hit.w, ray);
+    if (it.wvlsLost) wvl0 = 0.f;
+    int mat = w.sc.primMaterial ? PG_LD(w.sc.primMaterial + prim) : -1;
+    bool alive = false;
+    Ray next;
+    if (mat < 0) {
+        // no BSDF: Li(isect.SpawnRay(ray.d), ..., depth) -- before emission is added (directlighting.cpp:77-79)
+        next = spawnRay(it.p, it.pError, it.n, ray.d);
+        alive = true;
+    } else {
+        PathSampler smp;
+        smp.index = w.hIndex[slot];
+        smp.dim = w.dim[slot];
+        BSDF bsdf;
+        makeBSDF(it, PG_LD(w.sc.matTag + mat), w.sc.matParams + PBRTGPU_MAT_STRIDE * (size_t)mat, wvl0, &bsdf);
+        L += beta * hitLe(w.sc, prim, it.n, -ray.d);
+        const int nLights = w.sc.nLights;
+        if (nLights > 0) {
+            NeeRequest r;
+            bool culled;
+            if (w.directStrategy == PBRTGPU_DIRECT_ONE) {
+                int li = (int)(get1D(w.hal, smp) * nLights);
+                if (li > nLights - 1) li = nLights - 1;
+                float lightPdf = 1.f / nLights;
+                float uL0, uL1, uS0, uS1;
+                get2D(w.hal, smp, &uL0, &uL1);
+                get2D(w.hal, smp, &uS0, &uS1);
+                estimateDirectRays(w.sc, li, it, bsdf, uL0, uL1, uS0, uS1, spec(1.f), &r, &culled);
+                // EstimateDirect(...) / lightPdf, then the throughput
+                if (r.hasShadow) r.shadowContrib = beta * (r.shadowContrib / lightPdf);
+                if (r.hasClosest) r.closestContrib = beta * (r.closestContrib / lightPdf);
+                pushDirectRays(w, depth, slot, r);
+            } else {
+                int px, py, sampleNum;
+                slotToSample(w, slot, &px, &py, &sampleNum);
+                for (int j = 0; j < nLights; ++j) {
+                    int n = w.sc.lightNSamples ? PG_LD(w.sc.lightNSamples + j) : 1;
+                    int a = 2 * (vertices * nLights + j);  // Get2DArray is called twice per light per vertex
+                    if (a + 1 < w.nSampleArrays) {
+                        for (int k = 0; k < n; ++k) {
+                            float uL0, uL1, uS0, uS1;
+                            arraySample2D(w.hal, smp.index, sampleNum, a, n, k, &uL0, &uL1);
+                            arraySample2D(w.hal, smp.index, sampleNum, a + 1, n, k, &uS0, &uS1);
+                            estimateDirectRays(w.sc, j, it, bsdf, uL0, uL1, uS0, uS1, spec(1.f), &r, &culled);
+                            // L += Ld / nSamples with Ld the sum over k; here term by term
+                            if (r.hasShadow) r.shadowContrib = beta * (r.shadowContrib / (float)n);
+                            if (r.hasClosest) r.closestContrib = beta * (r.closestContrib / (float)n);
+                            pushDirectRays(w, depth, slot, r);
+                        }
+                    } else {  // the arrays are used up (vertices behind material-less boundaries): single samples
+                        float uL0, uL1, uS0, uS1;
+                        get2D(w.hal, smp, &uL0, &uL1);
+                        get2D(w.hal, smp, &uS0, &uS1);
+                        estimateDirectRays(w.sc, j, it, bsdf, uL0, uL1, uS0, uS1, spec(1.f), &r, &culled);
+                        if (r.hasShadow) r.shadowContrib = beta * r.shadowContrib;
+                        if (r.hasClosest) r.closestContrib = beta * r.closestContrib;
+                        pushDirectRays(w, depth, slot, r);
+                    }
+                }
+            }
+        }
+        if (bounces + 1 < w.maxDepth) {
+            V3 wo = -ray.d, wi = v3(0, 0, 0);
+            float pdf, u0, u1;
+            int sampled;
+            get2D(w.hal, smp, &u0, &u1);
+            Spec f = bsdfSampleF(bsdf, wo, &wi, u0, u1, &pdf, BSDF_REFLECTION | BSDF_SPECULAR, &sampled);
+            if (pdf > 0.f && !isBlack(f) && absDot(wi, it.ns) != 0.f) {
+                beta *= f * absDot(wi, it.ns) / pdf;
+                next = spawnRay(it.p, it.pError, it.n, wi);
+                ++bounces;
+                alive = true;
+            }
+        }
+        w.dim[slot] = smp.dim;
+    }
+    w.L[slot] = f4(L.r, L.g, L.b, wvl0);
+    if (alive) {
+        w.beta[slot] = f4(beta.r, beta.g, beta.b, bq.w);
+        // bit 8 (specularBounce) stays set: every vertex of this integrator adds emission, and so does a miss
+        w.flags[slot] = (flags & ~0x3fffdff) | bounces | 256 | (((vertices + (mat >= 0 ? 1 : 0)) & 0xffff) << 10);
+        int np = atomicIncInt(&w.cnt->nActive[depth + 1]);
+        storeRay(w.rays[cur ^ 1], np, next);
+        w.qSlot[cur ^ 1][np] = slot;
+    }
+}
+
+// L[slot] += (r, g, b) from a resolve kernel.  One queue entry per slot and kernel (path integrator,
+// directlighting "one"): a plain read-modify-write, nobody else touches the slot.  Several entries per
+// slot (directlighting "all": one per light sample): float atomics.
+PG_HD void addRadiance(const WaveParams &w, int slot, float r, float g, float b) {
+    if (w.neeCapacity > w.nSlots) {
+        float *Lp = (float *)&w.L[slot];
+        atomicAddFloat(Lp, r);
+        atomicAddFloat(Lp + 1, g);
+        atomicAddFloat(Lp + 2, b);
+    } else {
+        F4 Lq = w.L[slot];
+        Lq.x += r, Lq.y += g, Lq.z += b;
+        w.L[slot] = Lq;
+    }
+}
+
 // ---- stage 4a: shadow rays.  Unoccluded -> the light sample counts.
 PG_HD void stageShadowResolve(const WaveParams &w, int pos, bool occluded) {
     if (occluded) return;
     F4 c = w.shadowContrib[pos];
     int slot = (int)floatToBits(c.w);
-    F4 Lq = w.L[slot];
-    Lq.x += c.x, Lq.y += c.y, Lq.z += c.z;
-    w.L[slot] = Lq;
+    addRadiance(w, slot, c.x, c.y, c.z);
 }
 
 // ---- stage 4b: closest-hit next-event rays (BSDF-sampled MIS ray, portal rays).
@@ -270,9 +407,7 @@ PG_HD void stageNeeResolve(const WaveParams &w, int pos) {
         Li = loadSpec(w.sc.lightParams + PBRTGPU_LIGHT_STRIDE * (size_t)light);
     PG_TRACE("  nee resolve slot=%d prim=%d Li=(%g %g %g) b=(%g %g %g)\n", slot, prim, Li.r, Li.g, Li.b, hit.y, hit.z, hit.w);
     if (isBlack(Li)) return;
-    F4 Lq = w.L[slot];
-    Lq.x += c.x * Li.r, Lq.y += c.y * Li.g, Lq.z += c.z * Li.b;
-    w.L[slot] = Lq;
+    addRadiance(w, slot, c.x * Li.r, c.y * Li.g, c.z * Li.b);
 }
 
 // ---- stage 5: scrub (integrator.cpp:592-613) + FilmTile::AddSample with atomics

@@ -187,6 +187,17 @@ __global__ void __launch_bounds__(BLOCK, PER_SM) k_shade_sync(WaveParams w, int 
     }
 }
 
+// Integrator "directlighting": one vertex per thread, the block re-synchronised at every vertex
+__global__ void __launch_bounds__(512, 1) k_shade_direct(WaveParams w, int depth, int cur) {
+    int n = w.cnt->nHit[depth];
+    int stride = gridDim.x * blockDim.x;
+    for (int base = blockIdx.x * blockDim.x; base < n; base += stride) {
+        int i = base + threadIdx.x;
+        __syncthreads();
+        if (i < n) stageShadeDirect(w, depth, cur, w.hitIdx[i]);
+    }
+}
+
 // escaped rays: only launched when the scene has an infinite light
 __global__ void __launch_bounds__(kStageBlock) k_miss(WaveParams w, int depth, int cur) {
     int n = w.cnt->nMiss[depth];

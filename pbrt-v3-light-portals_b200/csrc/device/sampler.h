@@ -18,11 +18,14 @@ namespace pg {
 
 constexpr int kHaltonMaxResolution = 128;  // halton.cpp:42
 
+constexpr int kArrayStartDim = 5;  // GlobalSampler::arrayStartDim (sampler.h:122) -- although this fork's camera sample uses 6 dimensions
+
 struct HaltonParams {
     int baseScales[2], baseExponents[2];
     int sampleStride;
     int multInverse[2];
     int sampleAtPixelCenter;
+    int arrayEndDim;               // GlobalSampler: dimensions [kArrayStartDim, arrayEndDim) hold the sample arrays (sampler.cpp:126-148)
     const int *primes;             // 1000 entries
     const int *primeSums;          // 1000 entries
     const unsigned long long *primeMagic;  // 1000 entries: floor(2^64 / p) + 1, so that a / p = mulhi64(a, magic) for a < 2^32
@@ -172,6 +175,7 @@ inline HaltonParams makeHaltonParams(const int sampleBounds[4], int sampleAtPixe
         h.multInverse[i] = (int)(m < 0 ? m + n : m);
     }
     h.sampleAtPixelCenter = sampleAtPixelCenter;
+    h.arrayEndDim = kArrayStartDim;  // no sample arrays requested
     h.primes = nullptr;
     h.primeSums = nullptr;
     h.primeMagic = nullptr;
@@ -184,11 +188,28 @@ struct PathSampler {
     long long index;
     int dim;
 };
-PG_HD float get1D(const HaltonParams &h, PathSampler &s) { return haltonSample(h, s.index, s.dim++); }
+// GlobalSampler::Get1D / Get2D (sampler.cpp:181-196), including the jump over the array dimensions.
+PG_HD float get1D(const HaltonParams &h, PathSampler &s) {
+    if (s.dim >= kArrayStartDim && s.dim < h.arrayEndDim) s.dim = h.arrayEndDim;
+    return haltonSample(h, s.index, s.dim++);
+}
 PG_HD void get2D(const HaltonParams &h, PathSampler &s, float *u0, float *u1) {
+    if (s.dim + 1 >= kArrayStartDim && s.dim < h.arrayEndDim) s.dim = h.arrayEndDim;
     *u0 = haltonSample(h, s.index, s.dim);
     *u1 = haltonSample(h, s.index, s.dim + 1);
     s.dim += 2;
+}
+
+// Element k of 2D sample array `a` for pixel sample `sampleNum` (GlobalSampler::StartPixel, sampler.cpp:138-148,
+// + Sampler::Get2DArray, sampler.cpp:113-118): array a lives in dimensions kArrayStartDim + 2a, +1 and is filled
+// from the pixel's samples j = 0 .. n * spp - 1; pixel sample s reads elements s * n .. s * n + n - 1.
+// `index` is the Halton index of pixel sample `sampleNum` (GetIndexForSample: offset + sampleNum * stride).
+PG_HD void arraySample2D(const HaltonParams &h, long long index, int sampleNum, int a, int n, int k, float *u0, float *u1) {
+    long long j = (long long)sampleNum * n + k;
+    long long idx = index + (j - sampleNum) * h.sampleStride;
+    int dim = kArrayStartDim + 2 * a;
+    *u0 = haltonSample(h, idx, dim);
+    *u1 = haltonSample(h, idx, dim + 1);
 }
 
 }  // namespace pg

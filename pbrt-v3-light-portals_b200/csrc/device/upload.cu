@@ -179,6 +179,13 @@ int pbrtgpu_upload_scene(pbrtgpu_ctx *ctx, const pbrtgpu_scene *s) {
     UP(s->light_prim, s->n_lights, &d.lightPrim);
     UP(s->light_strategy, s->n_lights, &d.lightStrategy);
     UP(s->light_portal_begin, s->light_portal_begin ? s->n_lights + 1 : 0, &d.lightPortalBegin);
+    UP(s->light_nsamples, s->light_nsamples ? s->n_lights : 0, &d.lightNSamples);
+    ctx->sumLightSamples = 0;
+    for (int i = 0; i < s->n_lights; ++i) {
+        int n = s->light_nsamples ? s->light_nsamples[i] : 1;
+        if (n < 1) return ctx->fail(PBRTGPU_ERR_INVALID, "light %d: nsamples must be positive", i);
+        ctx->sumLightSamples += n;
+    }
     std::vector<float> lightParams(s->light_params, s->light_params + (size_t)s->n_lights * PBRTGPU_LIGHT_STRIDE);
     for (int i = 0; i < s->n_lights; ++i)
         if (s->light_tag[i] == PBRTGPU_LIGHT_INFINITE) finishInfiniteLight(lightParams.data() + (size_t)i * PBRTGPU_LIGHT_STRIDE);

@@ -29,6 +29,8 @@ inline void fillWaveParams(const pbrtgpu_render_params *rp, WaveParams *w) {
     w->hal = makeHaltonParams(rp->sample_bounds, rp->sample_at_pixel_center);
     w->maxDepth = rp->max_depth;
     w->rrThreshold = rp->rr_threshold;
+    w->integrator = rp->integrator;
+    w->directStrategy = rp->direct_strategy;
     int sw = rp->sample_bounds[2] - rp->sample_bounds[0];
     w->tilesX = (sw + 15) / 16;
     w->shardIndex = rp->shard_index;
@@ -42,10 +44,26 @@ struct BatchPlan {
     int tilesPerBatch;
     int maxSlots;
     int depthIters;      // wavefront iterations per batch
+    int neeMult;         // light samples per vertex: the shadow / next-event queues hold maxSlots * neeMult entries
 };
 
-inline BatchPlan planBatches(const pbrtgpu_render_params *rp, long long targetSlots, bool hasNullMaterial) {
+// Light samples a vertex can ask for: 1 for the path integrator and directlighting "one", the sum of the
+// lights' nSamples for directlighting "all".  Sizes the shadow / next-event queues.
+inline int lightSamplesPerVertex(const pbrtgpu_render_params *rp, const pbrtgpu_scene *s) {
+    if (rp->integrator != PBRTGPU_INTEGRATOR_DIRECT || rp->direct_strategy != PBRTGPU_DIRECT_ALL) return 1;
+    long long sum = 0;
+    for (int i = 0; i < s->n_lights; ++i) sum += s->light_nsamples ? s->light_nsamples[i] : 1;
+    return (int)(sum < 1 ? 1 : sum);
+}
+// DirectLightingIntegrator::Preprocess (directlighting.cpp:45-61): two 2D arrays per light per depth
+inline int sampleArrayCount(const pbrtgpu_render_params *rp, int nLights) {
+    if (rp->integrator != PBRTGPU_INTEGRATOR_DIRECT || rp->direct_strategy != PBRTGPU_DIRECT_ALL) return 0;
+    return 2 * nLights * (rp->max_depth > 0 ? rp->max_depth : 0);
+}
+
+inline BatchPlan planBatches(const pbrtgpu_render_params *rp, long long targetSlots, bool hasNullMaterial, int neeMult = 1) {
     BatchPlan p;
+    targetSlots /= neeMult;
     int sw = rp->sample_bounds[2] - rp->sample_bounds[0], sh = rp->sample_bounds[3] - rp->sample_bounds[1];
     p.tilesX = (sw + 15) / 16;
     p.tilesY = (sh + 15) / 16;
@@ -64,7 +82,9 @@ inline BatchPlan planBatches(const pbrtgpu_render_params *rp, long long targetSl
     // a path makes at most maxDepth + 1 scene intersections; vertices on
     // material-less primitives do not count as bounces (path.cpp:108-113), so
     // leave room for a few of those when the scene has any
+    p.neeMult = neeMult;
     p.depthIters = rp->max_depth + 1 + (hasNullMaterial ? 8 : 0);
+    if (rp->integrator == PBRTGPU_INTEGRATOR_DIRECT) p.depthIters = (rp->max_depth > 1 ? rp->max_depth : 1) + (hasNullMaterial ? 8 : 0);
     if (p.depthIters > kMaxDepthSlots - 1) p.depthIters = kMaxDepthSlots - 1;  // stage d touches the counters of depth d + 1
     return p;
 }
@@ -77,6 +97,13 @@ enum WaveBuf {
 inline size_t waveBufBytesPerSlot(int b) {
     static const size_t sz[WB_COUNT] = {8, 4, 16, 16, 4, 8, 32, 32, 4, 4, 16, 32, 16, 32, 16, 8, 16, 1, 4, 4};
     return sz[b];
+}
+inline bool waveBufIsLightSampleQueue(int b) {
+    return b == WB_SHADOW_RAYS || b == WB_SHADOW_CONTRIB || b == WB_NEE_RAYS || b == WB_NEE_CONTRIB || b == WB_NEE_INFO || b == WB_NEE_HITS ||
+           b == WB_SHADOW_OCC;
+}
+inline size_t waveBufBytes(int b, const BatchPlan &p) {
+    return waveBufBytesPerSlot(b) * (size_t)p.maxSlots * (waveBufIsLightSampleQueue(b) ? (size_t)p.neeMult : 1);
 }
 inline void bindWaveBuffers(WaveParams *w, void *const bufs[WB_COUNT]) {
     w->hIndex = (long long *)bufs[WB_HINDEX];

@@ -159,7 +159,7 @@ void SceneApi::LightSource(const std::string &name, const ParamSet &params) {
     if (name == "infinite" || name == "exinfinite") {  // lights/infinite.cpp:176-186
         RGB L = params.findOneSpectrum("L", RGB(1.f)), s = params.findOneSpectrum("scale", RGB(1.f));
         std::string texmap = params.findOneString("mapname", "");
-        params.findOneInt("samples", params.findOneInt("nsamples", 1));
+        l.nSamples = std::max(1, params.findOneInt("samples", params.findOneInt("nsamples", 1)));
         if (!texmap.empty()) {
             hostError("LightSource \"infinite\": environment maps (\"mapname\") are not supported by the GPU path integrator");
             failed = true;
@@ -267,7 +267,7 @@ void SceneApi::Shape(const std::string &name, const ParamSet &params) {
             const ParamSet &lp = gs.areaLightParams;
             LightData l;
             RGB L = lp.findOneSpectrum("L", RGB(1.f)), s = lp.findOneSpectrum("scale", RGB(1.f));
-            lp.findOneInt("samples", lp.findOneInt("nsamples", 1));
+            l.nSamples = std::max(1, lp.findOneInt("samples", lp.findOneInt("nsamples", 1)));
             bool twoSided = lp.findOneBool("twosided", false);
             bool made = true;
             if (gs.areaLight == "area" || gs.areaLight == "diffuse") {

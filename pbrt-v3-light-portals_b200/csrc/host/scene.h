@@ -102,6 +102,7 @@ struct LightData {
     int tag = 0;
     int prim = -1;  // creation-order primitive carrying this area light
     int strategy = PBRTGPU_PORTAL_UNIFORM_LIGHT;
+    int nSamples = 1;  // Light::nSamples (light.cpp:52: max(1, nSamples))
     float params[PBRTGPU_LIGHT_STRIDE] = {0};
     std::vector<PortalData> portals;
 };
@@ -135,7 +136,7 @@ struct FlatScene {
     std::vector<float> planeParams, sphereParams;
     std::vector<int32_t> matTag;
     std::vector<float> matParams;
-    std::vector<int32_t> lightTag, lightPrim, lightStrategy, lightPortalBegin;
+    std::vector<int32_t> lightTag, lightPrim, lightStrategy, lightPortalBegin, lightNSamples;
     std::vector<float> lightParams, portalParams;
     float worldCenter[3] = {0, 0, 0}, worldRadius = 0;
     Bounds3 worldBound;

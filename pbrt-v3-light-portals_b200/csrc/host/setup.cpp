@@ -45,6 +45,7 @@ pbrtgpu_scene FlatScene::view() const {
     s.light_strategy = lightStrategy.data();
     s.light_portal_begin = lightPortalBegin.data();
     s.light_params = lightParams.data();
+    s.light_nsamples = lightNSamples.data();
     s.n_portals = (int32_t)(portalParams.size() / PBRTGPU_PORTAL_STRIDE);
     s.portal_params = portalParams.data();
     memcpy(s.world_center, worldCenter, sizeof(worldCenter));
@@ -147,6 +148,7 @@ bool flattenScene(const SceneDesc &desc, FlatScene *out, std::string *err) {
         fs.lightTag.push_back(l.tag);
         fs.lightPrim.push_back(l.prim >= 0 ? slotOfPrim[l.prim] : -1);
         fs.lightStrategy.push_back(l.strategy);
+        fs.lightNSamples.push_back(l.nSamples);
         fs.lightParams.insert(fs.lightParams.end(), l.params, l.params + PBRTGPU_LIGHT_STRIDE);
         for (auto &p : l.portals) {
             float rec[PBRTGPU_PORTAL_STRIDE] = {0};
@@ -238,8 +240,8 @@ static bool makeFilterTable(const SceneDesc &d, float radius[2], float table[256
 bool makeRenderSetup(const SceneDesc &d, RenderSetup *out) {
     pbrtgpu_render_params &rp = out->params;
     memset(&rp, 0, sizeof(rp));
-    if (d.integratorName != "path") {
-        hostError("Integrator \"%s\" is not the plugin this library replaces (only Integrator \"path\")", d.integratorName.c_str());
+    if (d.integratorName != "path" && d.integratorName != "directlighting") {
+        hostError("Integrator \"%s\" is not a plugin this library replaces (Integrator \"path\" and \"directlighting\")", d.integratorName.c_str());
         return false;
     }
     if (d.cameraName != "perspective") {
@@ -337,13 +339,35 @@ bool makeRenderSetup(const SceneDesc &d, RenderSetup *out) {
                 hostError("Degenerate \"pixelbounds\" specified.");
         }
     }
-    rp.rr_threshold = ip.findOneFloat("rrthreshold", 1.);
-    std::string ls = ip.findOneString("lightsamplestrategy", "uniform");
-    if (ls == "uniform") rp.light_strategy = 0;
-    else if (ls == "power") rp.light_strategy = 1;
-    else {
-        hostError("Light sample distribution type \"%s\" is not supported by the GPU path integrator. Using \"uniform\".", ls.c_str());
-        rp.light_strategy = 0;
+    if (d.integratorName == "directlighting") {
+        // CreateDirectLightingIntegrator, directlighting.cpp:100-137
+        rp.integrator = PBRTGPU_INTEGRATOR_DIRECT;
+        // With allowMultipleLobes = false (integrator.cpp:615) glass is SpecularReflection + SpecularTransmission,
+        // and Li recurses into BOTH (directlighting.cpp:91-95): a tree of rays, not a path.  Not built yet.
+        for (auto &m : d.materials)
+            if (m.tag == PBRTGPU_MAT_GLASS || m.tag == PBRTGPU_MAT_DISPERSIVE_GLASS) {
+                hostError("Integrator \"directlighting\": materials with specular transmission (glass, dispersive_glass) are not supported "
+                          "by the GPU integrator (its specular recursion follows reflection only)");
+                return false;
+            }
+        std::string st = ip.findOneString("strategy", "all");
+        if (st == "one") rp.direct_strategy = PBRTGPU_DIRECT_ONE;
+        else if (st == "all") rp.direct_strategy = PBRTGPU_DIRECT_ALL;
+        else {
+            hostWarning("Strategy \"%s\" for direct lighting unknown. Using \"all\".", st.c_str());
+            rp.direct_strategy = PBRTGPU_DIRECT_ALL;
+        }
+        rp.rr_threshold = 1.f;
+    } else {
+        rp.integrator = PBRTGPU_INTEGRATOR_PATH;
+        rp.rr_threshold = ip.findOneFloat("rrthreshold", 1.);
+        std::string ls = ip.findOneString("lightsamplestrategy", "uniform");
+        if (ls == "uniform") rp.light_strategy = 0;
+        else if (ls == "power") rp.light_strategy = 1;
+        else {
+            hostError("Light sample distribution type \"%s\" is not supported by the GPU path integrator. Using \"uniform\".", ls.c_str());
+            rp.light_strategy = 0;
+        }
     }
     ip.reportUnused();
     rp.shard_index = 0, rp.shard_count = 1;

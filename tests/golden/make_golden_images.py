@@ -24,6 +24,11 @@ CASES = {
     "portal_room_portal": ("portal_room.pbrt", {"STRATEGY": "portal"}),
     "portal_room_projection": ("portal_room.pbrt", {"STRATEGY": "projection"}),
     "tri_soup": ("tri_soup.pbrt", {}),
+    # Integrator "directlighting": UniformSampleAllLights with sample arrays, and UniformSampleOneLight
+    "direct_all": ("direct_mixed.pbrt", {"DIRECT_STRATEGY": "all"}),
+    "direct_one": ("direct_mixed.pbrt", {"DIRECT_STRATEGY": "one"}),
+    # the portal room under directlighting "all" (how the fork's own scenes use portals)
+    "portal_room_direct": ("portal_room.pbrt", {"STRATEGY": "portal", 'Integrator "path" "integer maxdepth" [4]': 'Integrator "directlighting"'}),
 }
 
 

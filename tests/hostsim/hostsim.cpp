@@ -102,6 +102,7 @@ extern "C" int hostsim_render(void *p, const pbrtgpu_render_params *rp, float *f
     sc.matTag = s->mat_tag, sc.matParams = s->mat_params;
     sc.lightTag = s->light_tag, sc.lightPrim = s->light_prim, sc.lightStrategy = s->light_strategy;
     sc.lightPortalBegin = s->light_portal_begin, sc.portalParams = s->portal_params;
+    sc.lightNSamples = s->light_nsamples;
     std::vector<float> lightParams(s->light_params, s->light_params + (size_t)s->n_lights * PBRTGPU_LIGHT_STRIDE);
     for (int i = 0; i < s->n_lights; ++i)
         if (s->light_tag[i] == PBRTGPU_LIGHT_INFINITE) finishInfiniteLight(lightParams.data() + (size_t)i * PBRTGPU_LIGHT_STRIDE);
@@ -128,7 +129,9 @@ extern "C" int hostsim_render(void *p, const pbrtgpu_render_params *rp, float *f
     w.sc = sc;
     std::vector<unsigned long long> magic = primeMagics(primes);
     w.hal.primes = primes.data(), w.hal.primeSums = sums.data(), w.hal.perms = perms.data(), w.hal.primeMagic = magic.data();
-    BatchPlan pl = planBatches(rp, 1 << 18, nullMat);
+    BatchPlan pl = planBatches(rp, 1 << 18, nullMat, lightSamplesPerVertex(rp, s));
+    w.nSampleArrays = sampleArrayCount(rp, s->n_lights);
+    w.hal.arrayEndDim = kArrayStartDim + 2 * w.nSampleArrays;
     const int *cb = rp->cropped_bounds;
     size_t nPix = (size_t)(cb[2] - cb[0]) * (cb[3] - cb[1]);
     std::vector<float> film(nPix * 4, 0.f);
@@ -137,7 +140,7 @@ extern "C" int hostsim_render(void *p, const pbrtgpu_render_params *rp, float *f
     std::vector<std::vector<char>> store(WB_COUNT);
     void *bufs[WB_COUNT];
     for (int b = 0; b < WB_COUNT; ++b) {
-        store[b].resize(waveBufBytesPerSlot(b) * (size_t)pl.maxSlots + 16);
+        store[b].resize(waveBufBytes(b, pl) + 16);
         bufs[b] = store[b].data();
     }
     bindWaveBuffers(&w, bufs);
@@ -151,6 +154,7 @@ extern "C" int hostsim_render(void *p, const pbrtgpu_render_params *rp, float *f
             int nt = std::min(pl.tilesPerBatch, pl.shardTiles - t0);
             w.tileBegin = t0;
             w.nSlots = nt * 256 * w.sppCount;
+            w.neeCapacity = w.nSlots * pl.neeMult;
             memset(&cnt, 0, sizeof(cnt));
             parallelFor(w.nSlots, threads, [&](int64_t a, int64_t b) { for (int64_t i = a; i < b; ++i) stageRaygen(w, (int)i); });
             int cur = 0;
@@ -169,7 +173,12 @@ extern "C" int hostsim_render(void *p, const pbrtgpu_render_params *rp, float *f
                     }
                 });
                 parallelFor(cnt.nMiss[d], threads, [&](int64_t a, int64_t b) { for (int64_t i = a; i < b; ++i) stageMiss(w, cur, w.missIdx[i]); });
-                parallelFor(cnt.nHit[d], threads, [&](int64_t a, int64_t b) { for (int64_t i = a; i < b; ++i) stageShade(w, d, cur, w.hitIdx[i]); });
+                parallelFor(cnt.nHit[d], threads, [&](int64_t a, int64_t b) { 
+                    for (int64_t i = a; i < b; ++i) {
+                        if (w.integrator == PBRTGPU_INTEGRATOR_DIRECT) stageShadeDirect(w, d, cur, w.hitIdx[i]);
+                        else stageShade(w, d, cur, w.hitIdx[i]);
+                    }
+                });
                 parallelFor(cnt.nShadow[d], threads, [&](int64_t a, int64_t b) {
                     for (int64_t i = a; i < b; ++i) {
                         Ray ray = loadRay(w.shadowRays, (int)i);

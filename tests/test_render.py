@@ -86,7 +86,10 @@ def test_spp_ranges_partition_the_samples(pkg, hostsim_lib, golden):
 
 @pytest.mark.parametrize("name,kw", [("cornell-path.pbrt", dict(spp=4, res=(64, 64))),
                                      ("killeroo-path.pbrt", dict(spp=2, res=(80, 80))),
-                                     ("lamp/lamp.pbrt", dict(spp=2, res=(64, 64), integrator='Integrator "path"'))])
+                                     ("lamp/lamp.pbrt", dict(spp=2, res=(64, 64), integrator='Integrator "path"')),
+                                     # the fork's own portal scenes as shipped: Integrator "directlighting" (strategy "all")
+                                     ("lamp/lamp.pbrt", dict(spp=2, res=(64, 64))),
+                                     ("creeper/sandbox.pbrt", dict(spp=2, res=(64, 64)))])
 def test_reference_scenes_against_live_reference(pkg, hostsim_lib, name, kw, tmp_path):
     """Where oracle/_ref is present: BASELINE.json's scenes (reduced size), rendered by the reference now."""
     import subprocess
@@ -109,6 +112,15 @@ def test_reference_scenes_against_live_reference(pkg, hostsim_lib, name, kw, tmp
     rgb, _, _ = util.hostsim_render(hostsim_lib, hs)
     s = util.image_stats(rgb, read_pfm(out))
     assert s["rel_rmse"] <= CPU_TOL, s
+
+
+def test_directlighting_refuses_specular_transmission(pkg):
+    """DirectLightingIntegrator::Li recurses into reflection AND transmission (directlighting.cpp:91-95): a tree.
+    The GPU integrator follows reflection only and says so instead of rendering something else."""
+    text = scene_text("box_glass").replace('Integrator "path"', 'Integrator "directlighting"')
+    assert 'Integrator "directlighting"' in text
+    with pytest.raises(pkg.PbrtGpuError):
+        pkg.HostScene(text=text, base_dir=os.path.join(ROOT, "tests", "scenes"))
 
 
 def test_halton_first_dimensions_known_answers(pkg, hostsim_lib):

@@ -74,6 +74,24 @@ PG_HD_NOINLINE Spec lightSampleLi(const DevScene &sc, int li, const SurfInt &it,
         pL->p = it.p + *wi * (2 * sc.worldRadius);
         return L;
     }
+    if (tag == PBRTGPU_LIGHT_SPOT) {  // SpotLight::Sample_Li + Falloff, spot.cpp:51-73
+        V3 pLight = loadV3(lp + 3);
+        *wi = normalize(pLight - it.p);
+        *pdf = 1.f;
+        pL->p = pLight;
+        V3 w = -*wi;
+        const float *m = lp + 24;  // WorldToLight applied to a vector
+        V3 wl = normalize(v3(m[0] * w.x + m[1] * w.y + m[2] * w.z, m[4] * w.x + m[5] * w.y + m[6] * w.z, m[8] * w.x + m[9] * w.y + m[10] * w.z));
+        float cosTheta = wl.z, cosTotalWidth = PG_LD(lp + 6), cosFalloffStart = PG_LD(lp + 7);
+        float falloff;
+        if (cosTheta < cosTotalWidth) falloff = 0;
+        else if (cosTheta >= cosFalloffStart) falloff = 1;
+        else {
+            float delta = (cosTheta - cosTotalWidth) / (cosFalloffStart - cosTotalWidth);
+            falloff = (delta * delta) * (delta * delta);
+        }
+        return loadSpec(lp) * falloff / distanceSquared(pLight, it.p);
+    }
     if (tag == PBRTGPU_LIGHT_POINT) {
         V3 pLight = loadV3(lp + 3);
         *wi = normalize(pLight - it.p);
@@ -165,7 +183,7 @@ PG_HD_NOINLINE void estimateDirectRays(const DevScene &sc, int li, const SurfInt
         return;
     }
     const int flagsNS = BSDF_ALL & ~BSDF_SPECULAR;
-    bool isDelta = tag == PBRTGPU_LIGHT_POINT || tag == PBRTGPU_LIGHT_DISTANT;
+    bool isDelta = tag == PBRTGPU_LIGHT_POINT || tag == PBRTGPU_LIGHT_DISTANT || tag == PBRTGPU_LIGHT_SPOT;
     V3 wi = v3(0, 0, 0);  // Vector3f() is zero-initialised
     float lightPdf = 0, scatteringPdf = 0;
     ShapeSample pL;

@@ -110,7 +110,7 @@ PG_HD void stageShadePhased(const WaveParams &w, int depth, int cur, int pos, bo
     // ---- phase 3: sample the light (EstimateDirect, integrator.cpp:133-141); portal lights take their own estimator
     const bool portal = nee && lightTag == PBRTGPU_LIGHT_PORTAL_AREA;
     const bool stock = nee && !portal;
-    const bool isDelta = lightTag == PBRTGPU_LIGHT_POINT || lightTag == PBRTGPU_LIGHT_DISTANT;
+    const bool isDelta = lightTag == PBRTGPU_LIGHT_POINT || lightTag == PBRTGPU_LIGHT_DISTANT || lightTag == PBRTGPU_LIGHT_SPOT;
     V3 wi = v3(0, 0, 0);  // Vector3f() is zero-initialised
     float lightPdf = 0, scatteringPdf = 0;
     ShapeSample pL;

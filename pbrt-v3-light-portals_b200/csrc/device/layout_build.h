@@ -172,6 +172,7 @@ inline void buildLightDistribution(const pbrtgpu_scene *s, int strategy, std::ve
             case PBRTGPU_LIGHT_PORTAL_AREA: P = (lp[3] != 0.f ? 2 : 1) * L * lp[4] * kPi; break;  // diffuse.cpp:65-67
             case PBRTGPU_LIGHT_INFINITE: P = kPi * R * R * infiniteLookup(L, .5f, .5f); break;    // infinite.cpp:86-90
             case PBRTGPU_LIGHT_POINT: P = 4 * kPi * L; break;                                     // point.cpp:57
+            case PBRTGPU_LIGHT_SPOT: P = L * 2 * kPi * (1 - .5f * (lp[7] + lp[6])); break;        // spot.cpp:75-77
             default: P = L * kPi * R * R; break;                                                  // distant.cpp:65-67
             }
             (*func)[i] = luminance(P);

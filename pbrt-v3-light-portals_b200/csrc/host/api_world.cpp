@@ -177,6 +177,25 @@ void SceneApi::LightSource(const std::string &name, const ParamSet &params) {
         l.tag = PBRTGPU_LIGHT_POINT;
         put3(l.params, I * s);
         l.params[3] = pLight.x, l.params[4] = pLight.y, l.params[5] = pLight.z;
+    } else if (name == "spot") {  // lights/spot.cpp:105-125
+        RGB I = params.findOneSpectrum("I", RGB(1.f)), s = params.findOneSpectrum("scale", RGB(1.f));
+        float coneangle = params.findOneFloat("coneangle", 30.f), conedelta = params.findOneFloat("conedeltaangle", 5.f);
+        V3 from = params.findOnePoint3("from", v3(0, 0, 0)), to = params.findOnePoint3("to", v3(0, 0, 1));
+        V3 dir = normalize(to - from), du, dv;
+        coordinateSystem(dir, &du, &dv);
+        M44 dz = m44Identity();
+        dz.m[0][0] = du.x, dz.m[0][1] = du.y, dz.m[0][2] = du.z;
+        dz.m[1][0] = dv.x, dz.m[1][1] = dv.y, dz.m[1][2] = dv.z;
+        dz.m[2][0] = dir.x, dz.m[2][1] = dir.y, dz.m[2][2] = dir.z;
+        Xform l2w = xfMul(xfMul(ctm, xfTranslate(from)), xfInverse(xfFromMatrix(dz)));
+        V3 pLight = xformPoint(l2w.m, v3(0, 0, 0));
+        l.tag = PBRTGPU_LIGHT_SPOT;
+        put3(l.params, I * s);
+        l.params[3] = pLight.x, l.params[4] = pLight.y, l.params[5] = pLight.z;
+        l.params[6] = std::cos(coneangle * (kPi / 180));               // cosTotalWidth = cos(Radians(totalWidth))
+        l.params[7] = std::cos((coneangle - conedelta) * (kPi / 180));  // cosFalloffStart
+        memcpy(l.params + 8, &l2w.m.m[0][0], 16 * sizeof(float));
+        memcpy(l.params + 24, &l2w.mInv.m[0][0], 16 * sizeof(float));
     } else if (name == "distant") {  // lights/distant.cpp
         RGB L = params.findOneSpectrum("L", RGB(1.f)), s = params.findOneSpectrum("scale", RGB(1.f));
         V3 from = params.findOnePoint3("from", v3(0, 0, 0)), to = params.findOnePoint3("to", v3(0, 0, 1));

@@ -39,11 +39,20 @@ struct Lobe {
     float etaA, etaB;  // dielectric Fresnel (etaI, etaT) / transmission indices
 };
 
+struct MatLobes {  // what ComputeScatteringFunctions adds for one material (bsdf_eval.h:makeMaterialLobes)
+    int nLobes;
+    float eta;       // BSDF::eta
+    int dispersive;  // eta (and every lobe's etaT) follows the path's wavelength
+    int pad;
+    Lobe lobes[2];
+};
+
 struct BSDF {
     V3 ns, ng, ss, ts;
     float eta;
+    float etaOverride;  // 0, or etaT of all lobes (dispersive_glass)
     int nLobes;
-    Lobe lobes[2];
+    const Lobe *lobes;  // into the material table
 };
 
 // ---- local-frame trigonometry, reflection.h:52-92

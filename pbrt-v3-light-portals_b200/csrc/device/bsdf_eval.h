@@ -6,26 +6,26 @@ namespace pg {
 
 PG_HD bool lobeMatches(const Lobe &l, int flags) { return (l.type & flags) == l.type; }  // BxDF::MatchesFlags
 
-PG_HD Spec microReflF(const Lobe &l, V3 wo, V3 wi) {  // MicrofacetReflection::f
+PG_HD Spec microReflF(const Lobe &l, float etaB, V3 wo, V3 wi) {  // MicrofacetReflection::f
     float cosThetaO = absCosTheta(wo), cosThetaI = absCosTheta(wi);
     V3 wh = wi + wo;
     if (cosThetaI == 0 || cosThetaO == 0) return spec(0.f);
     if (wh.x == 0 && wh.y == 0 && wh.z == 0) return spec(0.f);
     wh = normalize(wh);
     float cosI = dot(wi, faceforward(wh, v3(0, 0, 1)));
-    Spec F = l.kind == LOBE_MICRO_REFL_COND ? frConductor(fabsf(cosI), spec(1.f), l.T, l.K) : spec(frDielectric(cosI, l.etaA, l.etaB));
+    Spec F = l.kind == LOBE_MICRO_REFL_COND ? frConductor(fabsf(cosI), spec(1.f), l.T, l.K) : spec(frDielectric(cosI, l.etaA, etaB));
     return l.R * trD(l.a, l.b, wh) * trG(l.a, l.b, wo, wi) * F / (4 * cosThetaI * cosThetaO);
 }
 
-PG_HD Spec microTransF(const Lobe &l, V3 wo, V3 wi) {  // MicrofacetTransmission::f, TransportMode::Radiance
+PG_HD Spec microTransF(const Lobe &l, float etaB, V3 wo, V3 wi) {  // MicrofacetTransmission::f, TransportMode::Radiance
     if (sameHemisphere(wo, wi)) return spec(0.f);
     float cosThetaO = cosTheta(wo), cosThetaI = cosTheta(wi);
     if (cosThetaI == 0 || cosThetaO == 0) return spec(0.f);
-    float eta = cosTheta(wo) > 0 ? (l.etaB / l.etaA) : (l.etaA / l.etaB);
+    float eta = cosTheta(wo) > 0 ? (etaB / l.etaA) : (l.etaA / etaB);
     V3 wh = normalize(wo + wi * eta);
     if (wh.z < 0) wh = -wh;
     if (dot(wo, wh) * dot(wi, wh) > 0) return spec(0.f);
-    float F = frDielectric(dot(wo, wh), l.etaA, l.etaB);
+    float F = frDielectric(dot(wo, wh), l.etaA, etaB);
     float sqrtDenom = dot(wo, wh) + eta * dot(wi, wh);
     float factor = 1 / eta;
     return (spec(1.f) - spec(F)) * l.R *
@@ -33,9 +33,9 @@ PG_HD Spec microTransF(const Lobe &l, V3 wo, V3 wi) {  // MicrofacetTransmission
                  (cosThetaI * cosThetaO * sqrtDenom * sqrtDenom));
 }
 
-PG_HD float microTransPdf(const Lobe &l, V3 wo, V3 wi) {
+PG_HD float microTransPdf(const Lobe &l, float etaB, V3 wo, V3 wi) {
     if (sameHemisphere(wo, wi)) return 0;
-    float eta = cosTheta(wo) > 0 ? (l.etaB / l.etaA) : (l.etaA / l.etaB);
+    float eta = cosTheta(wo) > 0 ? (etaB / l.etaA) : (l.etaA / etaB);
     V3 wh = normalize(wo + wi * eta);
     if (dot(wo, wh) * dot(wi, wh) > 0) return 0;
     float sqrtDenom = dot(wo, wh) + eta * dot(wi, wh);
@@ -63,18 +63,18 @@ PG_HD Spec orenNayarF(const Lobe &l, V3 wo, V3 wi) {
     return l.R * kInvPi * (l.a + l.b * maxCos * sinAlpha * tanBeta);
 }
 
-PG_HD_NOINLINE Spec lobeF(const Lobe &l, V3 wo, V3 wi) {
+PG_HD_NOINLINE Spec lobeF(const Lobe &l, float etaB, V3 wo, V3 wi) {
     switch (l.kind) {
     case LOBE_LAMBERT: return l.R * kInvPi;
     case LOBE_OREN_NAYAR: return orenNayarF(l, wo, wi);
     case LOBE_MICRO_REFL:
-    case LOBE_MICRO_REFL_COND: return microReflF(l, wo, wi);
-    case LOBE_MICRO_TRANS: return microTransF(l, wo, wi);
+    case LOBE_MICRO_REFL_COND: return microReflF(l, etaB, wo, wi);
+    case LOBE_MICRO_TRANS: return microTransF(l, etaB, wo, wi);
     default: return spec(0.f);  // specular lobes
     }
 }
 
-PG_HD_NOINLINE float lobePdf(const Lobe &l, V3 wo, V3 wi) {
+PG_HD_NOINLINE float lobePdf(const Lobe &l, float etaB, V3 wo, V3 wi) {
     switch (l.kind) {
     case LOBE_LAMBERT:
     case LOBE_OREN_NAYAR: return sameHemisphere(wo, wi) ? absCosTheta(wi) * kInvPi : 0;
@@ -84,20 +84,20 @@ PG_HD_NOINLINE float lobePdf(const Lobe &l, V3 wo, V3 wi) {
         V3 wh = normalize(wo + wi);
         return trPdf(l.a, l.b, wo, wh) / (4 * dot(wo, wh));
     }
-    case LOBE_MICRO_TRANS: return microTransPdf(l, wo, wi);
+    case LOBE_MICRO_TRANS: return microTransPdf(l, etaB, wo, wi);
     default: return 0;
     }
 }
 
 // BxDF::Sample_f of each lobe; *pdf must be 0 on entry (BSDF::Sample_f sets it).
-PG_HD_NOINLINE Spec lobeSample(const Lobe &l, V3 wo, float u0, float u1, V3 *wi, float *pdf, int *sampledType) {
+PG_HD_NOINLINE Spec lobeSample(const Lobe &l, float etaB, V3 wo, float u0, float u1, V3 *wi, float *pdf, int *sampledType) {
     switch (l.kind) {
     case LOBE_LAMBERT:
     case LOBE_OREN_NAYAR:
         *wi = cosineSampleHemisphere(u0, u1);
         if (wo.z < 0) wi->z *= -1;
-        *pdf = lobePdf(l, wo, *wi);
-        return lobeF(l, wo, *wi);
+        *pdf = lobePdf(l, etaB, wo, *wi);
+        return lobeF(l, etaB, wo, *wi);
     case LOBE_MICRO_REFL:
     case LOBE_MICRO_REFL_COND: {
         if (wo.z == 0) return spec(0.f);
@@ -106,19 +106,19 @@ PG_HD_NOINLINE Spec lobeSample(const Lobe &l, V3 wo, float u0, float u1, V3 *wi,
         *wi = reflectAbout(wo, wh);
         if (!sameHemisphere(wo, *wi)) return spec(0.f);
         *pdf = trPdf(l.a, l.b, wo, wh) / (4 * dot(wo, wh));
-        return microReflF(l, wo, *wi);
+        return microReflF(l, etaB, wo, *wi);
     }
     case LOBE_MICRO_TRANS: {
         if (wo.z == 0) return spec(0.f);
         V3 wh = trSampleWh(l.a, l.b, wo, u0, u1);
         if (dot(wo, wh) < 0) return spec(0.f);
-        float eta = cosTheta(wo) > 0 ? (l.etaA / l.etaB) : (l.etaB / l.etaA);
+        float eta = cosTheta(wo) > 0 ? (l.etaA / etaB) : (etaB / l.etaA);
         if (!refract(wo, wh, eta, wi)) return spec(0.f);
-        *pdf = microTransPdf(l, wo, *wi);
-        return microTransF(l, wo, *wi);
+        *pdf = microTransPdf(l, etaB, wo, *wi);
+        return microTransF(l, etaB, wo, *wi);
     }
     case LOBE_FRESNEL_SPECULAR: {
-        float F = frDielectric(cosTheta(wo), l.etaA, l.etaB);
+        float F = frDielectric(cosTheta(wo), l.etaA, etaB);
         if (u0 < F) {
             *wi = v3(-wo.x, -wo.y, wo.z);
             *sampledType = BSDF_SPECULAR | BSDF_REFLECTION;
@@ -126,8 +126,8 @@ PG_HD_NOINLINE Spec lobeSample(const Lobe &l, V3 wo, float u0, float u1, V3 *wi,
             return F * l.R / absCosTheta(*wi);
         }
         bool entering = cosTheta(wo) > 0;
-        float etaI = entering ? l.etaA : l.etaB;
-        float etaT = entering ? l.etaB : l.etaA;
+        float etaI = entering ? l.etaA : etaB;
+        float etaT = entering ? etaB : l.etaA;
         if (!refract(wo, faceforward(v3(0, 0, 1), wo), etaI / etaT, wi)) return spec(0.f);
         Spec ft = l.T * (1 - F);
         ft *= (etaI * etaI) / (etaT * etaT);
@@ -148,6 +148,8 @@ PG_HD V3 bsdfLocalToWorld(const BSDF &b, V3 v) {
     return v3(b.ss.x * v.x + b.ts.x * v.y + b.ns.x * v.z, b.ss.y * v.x + b.ts.y * v.y + b.ns.y * v.z,
               b.ss.z * v.x + b.ts.z * v.y + b.ns.z * v.z);
 }
+// etaT of lobe i: the material table's, or the per-path value of a dispersive material
+PG_HD float lobeEtaB(const BSDF &b, int i) { return b.etaOverride != 0.f ? b.etaOverride : b.lobes[i].etaB; }
 PG_HD int bsdfNumComponents(const BSDF &b, int flags) {
     int n = 0;
     for (int i = 0; i < b.nLobes; ++i)
@@ -163,7 +165,7 @@ PG_HD_NOINLINE Spec bsdfF(const BSDF &b, V3 woW, V3 wiW, int flags) {
     for (int i = 0; i < b.nLobes; ++i)
         if (lobeMatches(b.lobes[i], flags) && ((reflect && (b.lobes[i].type & BSDF_REFLECTION)) ||
                                                (!reflect && (b.lobes[i].type & BSDF_TRANSMISSION))))
-            f += lobeF(b.lobes[i], wo, wi);
+            f += lobeF(b.lobes[i], lobeEtaB(b, i), wo, wi);
     return f;
 }
 
@@ -176,7 +178,7 @@ PG_HD_NOINLINE float bsdfPdf(const BSDF &b, V3 woW, V3 wiW, int flags) {
     for (int i = 0; i < b.nLobes; ++i)
         if (lobeMatches(b.lobes[i], flags)) {
             ++matchingComps;
-            pdf += lobePdf(b.lobes[i], wo, wi);
+            pdf += lobePdf(b.lobes[i], lobeEtaB(b, i), wo, wi);
         }
     return matchingComps > 0 ? pdf / matchingComps : 0.f;
 }
@@ -208,7 +210,7 @@ PG_HD_NOINLINE Spec bsdfSampleF(const BSDF &b, V3 woW, V3 *wiW, float u0, float 
     }
     *pdf = 0;
     *sampledType = bx.type;
-    Spec f = lobeSample(bx, wo, uR, u1, &wi, pdf, sampledType);
+    Spec f = lobeSample(bx, lobeEtaB(b, which), wo, uR, u1, &wi, pdf, sampledType);
     if (*pdf == 0) {
         *sampledType = 0;
         return spec(0.f);
@@ -216,7 +218,7 @@ PG_HD_NOINLINE Spec bsdfSampleF(const BSDF &b, V3 woW, V3 *wiW, float u0, float 
     *wiW = bsdfLocalToWorld(b, wi);
     if (!(bx.type & BSDF_SPECULAR) && matchingComps > 1)
         for (int i = 0; i < b.nLobes; ++i)
-            if (i != which && lobeMatches(b.lobes[i], type)) *pdf += lobePdf(b.lobes[i], wo, wi);
+            if (i != which && lobeMatches(b.lobes[i], type)) *pdf += lobePdf(b.lobes[i], lobeEtaB(b, i), wo, wi);
     if (matchingComps > 1) *pdf /= matchingComps;
     if (!(bx.type & BSDF_SPECULAR)) {
         bool reflect = dot(*wiW, b.ng) * dot(woW, b.ng) > 0;
@@ -224,26 +226,27 @@ PG_HD_NOINLINE Spec bsdfSampleF(const BSDF &b, V3 woW, V3 *wiW, float u0, float 
         for (int i = 0; i < b.nLobes; ++i)
             if (lobeMatches(b.lobes[i], type) && ((reflect && (b.lobes[i].type & BSDF_REFLECTION)) ||
                                                   (!reflect && (b.lobes[i].type & BSDF_TRANSMISSION))))
-                f += lobeF(b.lobes[i], wo, wi);
+                f += lobeF(b.lobes[i], lobeEtaB(b, i), wo, wi);
     }
     return f;
 }
 
 // Material::ComputeScatteringFunctions for the material table of pbrtgpu.h
 // (allowMultipleLobes = true, TransportMode::Radiance, as path.cpp:107 calls it).
-// wvl0 = hero wavelength in nm, used by dispersive_glass only.
-PG_HD_NOINLINE void makeBSDF(const SurfInt &it, int tag, const float *mp, float wvl0, BSDF *b) {
-    b->ns = it.ns;
-    b->ng = it.n;
-    b->ss = normalize(it.dpdus);
-    b->ts = cross(b->ns, b->ss);
-    b->eta = 1;
-    b->nLobes = 0;
+//
+// Textures are constants, so which BxDFs a material adds and with what parameters is the same at
+// every vertex: makeMaterialLobes runs ONCE per material (at upload, on the host) and the kernels
+// read the result from a small table.  Per vertex only the shading frame is built -- and, for
+// dispersive_glass, the index of refraction of the path's hero wavelength.
+PG_HD void makeMaterialLobes(int tag, const float *mp, MatLobes *m) {
+    m->nLobes = 0;
+    m->eta = 1;
+    m->dispersive = 0;
     if (tag == PBRTGPU_MAT_MATTE) {
         Spec r = loadSpec(mp);
-        float sig = PG_LD(mp + 3);
+        float sig = mp[3];
         if (!isBlack(r)) {
-            Lobe &l = b->lobes[b->nLobes++];
+            Lobe &l = m->lobes[m->nLobes++];
             l.type = BSDF_REFLECTION | BSDF_DIFFUSE;
             l.R = r;
             if (sig == 0) l.kind = LOBE_LAMBERT;
@@ -258,37 +261,37 @@ PG_HD_NOINLINE void makeBSDF(const SurfInt &it, int tag, const float *mp, float 
     } else if (tag == PBRTGPU_MAT_PLASTIC) {
         Spec kd = loadSpec(mp), ks = loadSpec(mp + 3);
         if (!isBlack(kd)) {
-            Lobe &l = b->lobes[b->nLobes++];
+            Lobe &l = m->lobes[m->nLobes++];
             l.kind = LOBE_LAMBERT;
             l.type = BSDF_REFLECTION | BSDF_DIFFUSE;
             l.R = kd;
         }
         if (!isBlack(ks)) {
-            Lobe &l = b->lobes[b->nLobes++];
+            Lobe &l = m->lobes[m->nLobes++];
             l.kind = LOBE_MICRO_REFL;
             l.type = BSDF_REFLECTION | BSDF_GLOSSY;
             l.R = ks;
-            l.a = l.b = PG_LD(mp + 6);
+            l.a = l.b = mp[6];
             l.etaA = 1.5f, l.etaB = 1.f;
         }
     } else if (tag == PBRTGPU_MAT_GLASS || tag == PBRTGPU_MAT_DISPERSIVE_GLASS) {
         Spec R = loadSpec(mp), T = loadSpec(mp + 3);
         float eta;
-        if (tag == PBRTGPU_MAT_GLASS) eta = PG_LD(mp + 8);
-        else eta = PG_LD(mp + 8) + PG_LD(mp + 10) / (wvl0 * wvl0);  // cauchyB + cauchyC / lambda^2
-        b->eta = eta;
+        if (tag == PBRTGPU_MAT_GLASS) eta = mp[8];
+        else eta = 1.f, m->dispersive = 1;  // eta = cauchyB + cauchyC / lambda^2 per path: BSDF::etaOverride (makeBSDF)
+        m->eta = eta;
         if (isBlack(R) && isBlack(T)) return;
-        bool isSpecular = PG_LD(mp + 9) != 0.f;
+        bool isSpecular = mp[9] != 0.f;
         if (isSpecular) {
-            Lobe &l = b->lobes[b->nLobes++];
+            Lobe &l = m->lobes[m->nLobes++];
             l.kind = LOBE_FRESNEL_SPECULAR;
             l.type = BSDF_REFLECTION | BSDF_TRANSMISSION | BSDF_SPECULAR;
             l.R = R, l.T = T;
             l.etaA = 1.f, l.etaB = eta;
         } else {
-            float ax = PG_LD(mp + 6), ay = PG_LD(mp + 7);
+            float ax = mp[6], ay = mp[7];
             if (!isBlack(R)) {
-                Lobe &l = b->lobes[b->nLobes++];
+                Lobe &l = m->lobes[m->nLobes++];
                 l.kind = LOBE_MICRO_REFL;
                 l.type = BSDF_REFLECTION | BSDF_GLOSSY;
                 l.R = R;
@@ -296,7 +299,7 @@ PG_HD_NOINLINE void makeBSDF(const SurfInt &it, int tag, const float *mp, float 
                 l.etaA = 1.f, l.etaB = eta;
             }
             if (!isBlack(T)) {
-                Lobe &l = b->lobes[b->nLobes++];
+                Lobe &l = m->lobes[m->nLobes++];
                 l.kind = LOBE_MICRO_TRANS;
                 l.type = BSDF_TRANSMISSION | BSDF_GLOSSY;
                 l.R = T;
@@ -305,20 +308,37 @@ PG_HD_NOINLINE void makeBSDF(const SurfInt &it, int tag, const float *mp, float 
             }
         }
     } else if (tag == PBRTGPU_MAT_METAL) {  // materials/metal.cpp:60-82
-        Lobe &l = b->lobes[b->nLobes++];
+        Lobe &l = m->lobes[m->nLobes++];
         l.kind = LOBE_MICRO_REFL_COND;
         l.type = BSDF_REFLECTION | BSDF_GLOSSY;
         l.R = spec(1.f);
         l.T = loadSpec(mp), l.K = loadSpec(mp + 3);
-        l.a = PG_LD(mp + 6), l.b = PG_LD(mp + 7);
+        l.a = mp[6], l.b = mp[7];
     } else if (tag == PBRTGPU_MAT_MIRROR) {
         Spec R = loadSpec(mp);
         if (!isBlack(R)) {
-            Lobe &l = b->lobes[b->nLobes++];
+            Lobe &l = m->lobes[m->nLobes++];
             l.kind = LOBE_SPEC_REFL_NOOP;
             l.type = BSDF_REFLECTION | BSDF_SPECULAR;
             l.R = R;
         }
+    }
+}
+
+PG_HD_NOINLINE void makeBSDF(const SurfInt &it, const MatLobes *table, int mat, const float *mp, float wvl0, BSDF *b) {
+    b->ns = it.ns;
+    b->ng = it.n;
+    b->ss = normalize(it.dpdus);
+    b->ts = cross(b->ns, b->ss);
+    const MatLobes *m = table + mat;
+    b->lobes = m->lobes;
+    b->nLobes = PG_LD(&m->nLobes);
+    b->eta = PG_LD(&m->eta);
+    b->etaOverride = 0.f;
+    if (PG_LD(&m->dispersive)) {
+        float eta = PG_LD(mp + 8) + PG_LD(mp + 10) / (wvl0 * wvl0);  // cauchyB + cauchyC / lambda^2 (dispersive_glass.cpp:63-65)
+        b->eta = eta;
+        b->etaOverride = eta;
     }
 }
 

@@ -2,6 +2,7 @@
 #ifndef PG_DEVICE_CTX_SCENE_H
 #define PG_DEVICE_CTX_SCENE_H
 
+#include "bsdf.h"
 #include "bvh.h"
 
 namespace pg {
@@ -19,6 +20,7 @@ struct DevScene {
     const float *triS;   // 9 per slot or null
     const int *matTag;
     const float *matParams;
+    const MatLobes *matLobes;  // nMaterials entries, built at upload
     const int *lightTag;
     const int *lightPrim;
     const int *lightStrategy;

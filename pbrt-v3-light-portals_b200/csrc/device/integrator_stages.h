@@ -86,7 +86,7 @@ PG_HD void stageShadePhased(const WaveParams &w, int depth, int cur, int pos, bo
     if (scatter) {
         smp.index = w.hIndex[slot];
         smp.dim = w.dim[slot];
-        makeBSDF(it, PG_LD(w.sc.matTag + mat), w.sc.matParams + PBRTGPU_MAT_STRIDE * (size_t)mat, wvl0, &bsdf);
+        makeBSDF(it, w.sc.matLobes, mat, w.sc.matParams + PBRTGPU_MAT_STRIDE * (size_t)mat, wvl0, &bsdf);
     }
     sync();
 
@@ -288,7 +288,7 @@ PG_HD void stageShadeDirect(const WaveParams &w, int depth, int cur, int pos) {
         smp.index = w.hIndex[slot];
         smp.dim = w.dim[slot];
         BSDF bsdf;
-        makeBSDF(it, PG_LD(w.sc.matTag + mat), w.sc.matParams + PBRTGPU_MAT_STRIDE * (size_t)mat, wvl0, &bsdf);
+        makeBSDF(it, w.sc.matLobes, mat, w.sc.matParams + PBRTGPU_MAT_STRIDE * (size_t)mat, wvl0, &bsdf);
         L += beta * hitLe(w.sc, prim, it.n, -ray.d);
         const int nLights = w.sc.nLights;
         if (nLights > 0) {

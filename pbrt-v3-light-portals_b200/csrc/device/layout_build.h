@@ -155,6 +155,13 @@ inline void finishInfiniteLight(float *lp) {
 }
 
 
+// The per-material BxDF table (bsdf_eval.h:makeMaterialLobes), one entry per material.
+inline void buildMaterialLobes(const pbrtgpu_scene *s, std::vector<MatLobes> *out) {
+    out->resize(s->n_materials > 0 ? s->n_materials : 1);
+    memset(out->data(), 0, out->size() * sizeof(MatLobes));
+    for (int i = 0; i < s->n_materials; ++i) makeMaterialLobes(s->mat_tag[i], s->mat_params + (size_t)i * PBRTGPU_MAT_STRIDE, &(*out)[i]);
+}
+
 // PathIntegrator::Preprocess -> CreateLightSampleDistribution (core/lightdistrib.cpp:48-66,
 // 68-88; ComputeLightPowerDistribution core/integrator.cpp:44-50): the
 // Distribution1D the light is picked from.  strategy 0 = uniform, 1 = power.

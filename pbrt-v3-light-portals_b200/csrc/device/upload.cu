@@ -178,6 +178,11 @@ int pbrtgpu_upload_scene(pbrtgpu_ctx *ctx, const pbrtgpu_scene *s) {
     UP(s->light_tag, s->n_lights, &d.lightTag);
     UP(s->light_prim, s->n_lights, &d.lightPrim);
     UP(s->light_strategy, s->n_lights, &d.lightStrategy);
+    {
+        std::vector<MatLobes> lobes;
+        buildMaterialLobes(s, &lobes);
+        UP(lobes.data(), lobes.size(), &d.matLobes);
+    }
     UP(s->light_portal_begin, s->light_portal_begin ? s->n_lights + 1 : 0, &d.lightPortalBegin);
     UP(s->light_nsamples, s->light_nsamples ? s->n_lights : 0, &d.lightNSamples);
     ctx->sumLightSamples = 0;

@@ -103,6 +103,9 @@ extern "C" int hostsim_render(void *p, const pbrtgpu_render_params *rp, float *f
     sc.lightTag = s->light_tag, sc.lightPrim = s->light_prim, sc.lightStrategy = s->light_strategy;
     sc.lightPortalBegin = s->light_portal_begin, sc.portalParams = s->portal_params;
     sc.lightNSamples = s->light_nsamples;
+    std::vector<MatLobes> matLobes;
+    buildMaterialLobes(s, &matLobes);
+    sc.matLobes = matLobes.data();
     std::vector<float> lightParams(s->light_params, s->light_params + (size_t)s->n_lights * PBRTGPU_LIGHT_STRIDE);
     for (int i = 0; i < s->n_lights; ++i)
         if (s->light_tag[i] == PBRTGPU_LIGHT_INFINITE) finishInfiniteLight(lightParams.data() + (size_t)i * PBRTGPU_LIGHT_STRIDE);

@@ -61,7 +61,7 @@ struct pbrtgpu_ctx {
     bool traceFused = true;   // one traversal launch per depth for path + next-event + shadow rays
     bool shadeSync = true;
     int shadeBlock = 1024;
-    int fetchThreshold = 8;
+    int fetchThreshold = 12;
     int phaseBias = 16;
     int persistBlocksPerSM = pg::kPersistMinBlocks;
     int *dFetch = nullptr;  // queue cursor of the ray-batch entry points

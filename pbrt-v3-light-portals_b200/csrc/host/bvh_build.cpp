@@ -136,7 +136,150 @@ struct Builder {
     }
 };
 
-void flatten(const Builder &b, int nodeIdx, BuiltBVH *out) {
+// ---- HLBVH (BVHAccel::HLBVHBuild, bvh.cpp:404-464; emitLBVH :466-537; buildUpperSAH :539-638).
+// Morton codes of the centroids (10 bits per axis), a stable sort on them (the reference's LSD radix
+// sort is stable), one LBVH treelet per distinct value of the top 12 bits, a SAH tree over the treelet
+// roots.  The reference builds treelets in parallel and hands out leaf slots with an atomic counter,
+// so the NUMBERING of leaf slots depends on its thread schedule; the tree itself does not.  Treelets
+// are built here in order, which is the reference's numbering with --nthreads 1.
+inline uint32_t leftShift3(uint32_t x) {  // bvh.cpp:107-130
+    if (x == (1 << 10)) --x;
+    x = (x | (x << 16)) & 0x30000ff;
+    x = (x | (x << 8)) & 0x300f00f;
+    x = (x | (x << 4)) & 0x30c30c3;
+    x = (x | (x << 2)) & 0x9249249;
+    return x;
+}
+inline uint32_t encodeMorton3(V3 v) { return (leftShift3((uint32_t)v.z) << 2) | (leftShift3((uint32_t)v.y) << 1) | leftShift3((uint32_t)v.x); }
+
+struct MortonPrim {
+    int primitiveIndex;
+    uint32_t mortonCode;
+};
+
+struct HLBuilder {
+    const std::vector<PrimInfo> *info;
+    std::vector<BuildNode> nodes;
+    std::vector<int> ordered;
+    int maxPrimsInNode;
+
+    int emitLBVH(const MortonPrim *mp, int nPrimitives, int bitIndex) {
+        if (bitIndex == -1 || nPrimitives < maxPrimsInNode) {
+            int nodeIdx = (int)nodes.size();
+            nodes.emplace_back();
+            Bounds3 bounds;
+            int first = (int)ordered.size();
+            for (int i = 0; i < nPrimitives; ++i) {
+                ordered.push_back(mp[i].primitiveIndex);
+                bounds = unionB(bounds, (*info)[mp[i].primitiveIndex].bounds);
+            }
+            nodes[nodeIdx].firstPrimOffset = first;
+            nodes[nodeIdx].nPrimitives = nPrimitives;
+            nodes[nodeIdx].bounds = bounds;
+            return nodeIdx;
+        }
+        uint32_t mask = 1u << bitIndex;
+        if ((mp[0].mortonCode & mask) == (mp[nPrimitives - 1].mortonCode & mask)) return emitLBVH(mp, nPrimitives, bitIndex - 1);
+        int searchStart = 0, searchEnd = nPrimitives - 1;
+        while (searchStart + 1 != searchEnd) {
+            int mid = (searchStart + searchEnd) / 2;
+            if ((mp[searchStart].mortonCode & mask) == (mp[mid].mortonCode & mask)) searchStart = mid;
+            else searchEnd = mid;
+        }
+        int splitOffset = searchEnd;
+        int nodeIdx = (int)nodes.size();
+        nodes.emplace_back();
+        int c0 = emitLBVH(mp, splitOffset, bitIndex - 1);
+        int c1 = emitLBVH(mp + splitOffset, nPrimitives - splitOffset, bitIndex - 1);
+        BuildNode &n = nodes[nodeIdx];
+        n.child[0] = c0, n.child[1] = c1;
+        n.bounds = unionB(nodes[c0].bounds, nodes[c1].bounds);
+        n.splitAxis = bitIndex % 3;
+        n.nPrimitives = 0;
+        return nodeIdx;
+    }
+
+    int buildUpperSAH(std::vector<int> &roots, int start, int end) {
+        int nNodes = end - start;
+        if (nNodes == 1) return roots[start];
+        Bounds3 bounds;
+        for (int i = start; i < end; ++i) bounds = unionB(bounds, nodes[roots[i]].bounds);
+        Bounds3 centroidBounds;
+        for (int i = start; i < end; ++i) {
+            const Bounds3 &b = nodes[roots[i]].bounds;
+            centroidBounds = unionB(centroidBounds, (b.pMin + b.pMax) * 0.5f);
+        }
+        int dim = centroidBounds.maximumExtent();
+        // the reference CHECKs centroidBounds.pMax[dim] != pMin[dim] here and aborts otherwise (bvh.cpp:562)
+        constexpr int nBuckets = 12;
+        struct Bucket {
+            int count = 0;
+            Bounds3 bounds;
+        } buckets[nBuckets];
+        const float cMin = centroidBounds.pMin[dim], cMax = centroidBounds.pMax[dim];
+        auto bucketOf = [&](int root) {
+            const Bounds3 &b = nodes[root].bounds;
+            float centroid = (b.pMin[dim] + b.pMax[dim]) * 0.5f;
+            int k = (int)(nBuckets * ((centroid - cMin) / (cMax - cMin)));
+            if (k == nBuckets) k = nBuckets - 1;
+            return k;
+        };
+        for (int i = start; i < end; ++i) {
+            int k = bucketOf(roots[i]);
+            buckets[k].count++;
+            buckets[k].bounds = unionB(buckets[k].bounds, nodes[roots[i]].bounds);
+        }
+        float cost[nBuckets - 1];
+        for (int i = 0; i < nBuckets - 1; ++i) {
+            Bounds3 b0, b1;
+            int count0 = 0, count1 = 0;
+            for (int j = 0; j <= i; ++j) b0 = unionB(b0, buckets[j].bounds), count0 += buckets[j].count;
+            for (int j = i + 1; j < nBuckets; ++j) b1 = unionB(b1, buckets[j].bounds), count1 += buckets[j].count;
+            cost[i] = .125f + (count0 * b0.surfaceArea() + count1 * b1.surfaceArea()) / bounds.surfaceArea();
+        }
+        float minCost = cost[0];
+        int minCostSplitBucket = 0;
+        for (int i = 1; i < nBuckets - 1; ++i)
+            if (cost[i] < minCost) minCost = cost[i], minCostSplitBucket = i;
+        int *pmid = std::partition(&roots[start], &roots[end - 1] + 1, [&](int root) { return bucketOf(root) <= minCostSplitBucket; });
+        int mid = (int)(pmid - &roots[0]);
+        int nodeIdx = (int)nodes.size();
+        nodes.emplace_back();
+        int c0 = buildUpperSAH(roots, start, mid);
+        int c1 = buildUpperSAH(roots, mid, end);
+        BuildNode &n = nodes[nodeIdx];
+        n.child[0] = c0, n.child[1] = c1;
+        n.bounds = unionB(nodes[c0].bounds, nodes[c1].bounds);
+        n.splitAxis = dim;
+        n.nPrimitives = 0;
+        return nodeIdx;
+    }
+
+    int build() {
+        const std::vector<PrimInfo> &pi = *info;
+        Bounds3 bounds;
+        for (const PrimInfo &p : pi) bounds = unionB(bounds, p.centroid);
+        std::vector<MortonPrim> mp(pi.size());
+        const int mortonScale = 1 << 10;
+        for (size_t i = 0; i < pi.size(); ++i) {
+            mp[i].primitiveIndex = (int)pi[i].primitiveNumber;
+            V3 o = bounds.offset(pi[i].centroid);
+            mp[i].mortonCode = encodeMorton3(o * (float)mortonScale);
+        }
+        std::stable_sort(mp.begin(), mp.end(), [](const MortonPrim &a, const MortonPrim &b) { return a.mortonCode < b.mortonCode; });
+        std::vector<int> roots;
+        const uint32_t mask = 0x3ffc0000;
+        for (int start = 0, end = 1; end <= (int)mp.size(); ++end)
+            if (end == (int)mp.size() || ((mp[start].mortonCode & mask) != (mp[end].mortonCode & mask))) {
+                roots.push_back(emitLBVH(&mp[start], end - start, 29 - 12));
+                start = end;
+            }
+        return buildUpperSAH(roots, 0, (int)roots.size());
+    }
+};
+
+template <class B>
+void flatten(const B &b, int nodeIdx, BuiltBVH *out) {
     const BuildNode &n = b.nodes[nodeIdx];
     int my = (int)out->offset.size();
     const float bb[6] = {n.bounds.pMin.x, n.bounds.pMin.y, n.bounds.pMin.z, n.bounds.pMax.x, n.bounds.pMax.y, n.bounds.pMax.z};
@@ -162,12 +305,24 @@ BuiltBVH buildBVH(const std::vector<Bounds3> &primBounds, int maxPrimsInNode, Sp
     if (primBounds.empty()) return out;
     Builder b;
     b.maxPrimsInNode = std::min(255, maxPrimsInNode);
-    b.method = method == SplitMethod::HLBVH ? SplitMethod::SAH : method;
+    b.method = method;
     b.info.resize(primBounds.size());
     for (size_t i = 0; i < primBounds.size(); ++i) {
         b.info[i].primitiveNumber = i;
         b.info[i].bounds = primBounds[i];
         b.info[i].centroid = .5f * primBounds[i].pMin + .5f * primBounds[i].pMax;
+    }
+    if (method == SplitMethod::HLBVH) {
+        HLBuilder h;
+        h.info = &b.info;
+        h.maxPrimsInNode = b.maxPrimsInNode;
+        h.nodes.reserve(2 * primBounds.size());
+        h.ordered.reserve(primBounds.size());
+        int root = h.build();
+        out.bounds.reserve(6 * h.nodes.size());
+        flatten(h, root, &out);
+        out.orderedPrims = std::move(h.ordered);
+        return out;
     }
     b.nodes.reserve(2 * primBounds.size());
     b.ordered.reserve(primBounds.size());

@@ -54,6 +54,34 @@ def test_host_bvh_matches_reference_dump(soup):
     assert np.array_equal(util.bits(v.array("tri_p", v.n_prims, 9)), prims[:, 8:].copy().view(np.uint32).reshape(-1, 9))
 
 
+@pytest.mark.parametrize("method", ["hlbvh", "middle", "equal", "sah"])
+def test_host_bvh_split_methods_match_live_reference(pkg, ref_harness, method, tmp_path):
+    """Accelerator "bvh" "splitmethod": every method's tree, node for node and leaf slot for leaf slot, against a
+    dump of the reference's BVHAccel (HLBVHBuild bvh.cpp:404-638 included: Morton codes, treelets, upper SAH)."""
+    import subprocess
+    if not ref_harness:
+        pytest.skip("oracle/_ref not built")
+    src = scene_path("tri_soup.pbrt")
+    text = open(src).read().replace("WorldBegin", 'Accelerator "bvh" "string splitmethod" "%s"\nWorldBegin' % method, 1)
+    tmp = os.path.join(os.path.dirname(src), "_split_%s_%d.pbrt" % (method, os.getpid()))
+    open(tmp, "w").write(text)
+    try:
+        subprocess.check_call([ref_harness, "dump", tmp, str(tmp_path / "d")], stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+        hs = pkg.HostScene(tmp)
+    finally:
+        os.unlink(tmp)
+    nodes = np.fromfile(str(tmp_path / "d.nodes.bin"), dtype=np.uint8).reshape(-1, 32)
+    prims = np.fromfile(str(tmp_path / "d.prims.bin"), dtype=np.uint8).reshape(-1, 44)
+    v = hs.view
+    assert v.n_nodes == len(nodes) and v.n_prims == len(prims)
+    nprims = nodes[:, 28:30].copy().view(np.uint16).ravel()
+    assert np.array_equal(util.bits(v.array("bvh_bounds", v.n_nodes, 6)), nodes[:, :24].copy().view(np.uint32))
+    assert np.array_equal(v.array("bvh_offset", v.n_nodes), nodes[:, 24:28].copy().view(np.int32).ravel())
+    assert np.array_equal(v.array("bvh_nprims", v.n_nodes), nprims)
+    assert np.array_equal(v.array("bvh_axis", v.n_nodes)[nprims == 0], nodes[:, 30][nprims == 0])
+    assert np.array_equal(v.array("prim_orig_id", v.n_prims), prims[:, :4].copy().view(np.int32).ravel())
+
+
 def test_ray_generators_are_stable(soup, golden):
     for name, rays in ray_sets(soup.view).items():
         assert hashlib.sha256(rays.tobytes()).hexdigest() == str(golden[name + "_sha"]), name

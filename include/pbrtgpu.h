@@ -55,9 +55,10 @@ enum {
     PBRTGPU_MAT_GLASS = 3,            /* materials/glass.cpp:45-92   params Kr[3] Kt[3] ualpha valpha eta */
     PBRTGPU_MAT_DISPERSIVE_GLASS = 4, /* materials/dispersive_glass.cpp:48-123 params Kr[3] Kt[3] ualpha valpha etaMin etaMax */
     PBRTGPU_MAT_MIRROR = 5,           /* materials/mirror.cpp        params Kr[3] */
-    PBRTGPU_MAT_METAL = 6             /* materials/metal.cpp         params eta[3] k[3] ualpha valpha */
+    PBRTGPU_MAT_METAL = 6,            /* materials/metal.cpp         params eta[3] k[3] ualpha valpha */
+    PBRTGPU_MAT_UBER = 7              /* materials/uber.cpp:45-105   params Kd[3] Ks[3] Kr[3] Kt[3] opacity[3] ualpha valpha eta (all clamped) */
 };
-#define PBRTGPU_MAT_STRIDE 16 /* floats per material in mat_params */
+#define PBRTGPU_MAT_STRIDE 24 /* floats per material in mat_params */
 
 /* light tags */
 enum {

@@ -18,7 +18,7 @@ import numpy as np
 _PKG = os.path.dirname(os.path.abspath(__file__))
 _LIB = os.path.join(_PKG, "lib")
 
-MAT_STRIDE, LIGHT_STRIDE, PLANE_STRIDE, SPHERE_STRIDE, PORTAL_STRIDE = 16, 48, 48, 48, 16
+MAT_STRIDE, LIGHT_STRIDE, PLANE_STRIDE, SPHERE_STRIDE, PORTAL_STRIDE = 24, 48, 48, 48, 16
 N_HALTON_PERMS = 3682913
 
 

@@ -27,7 +27,9 @@ enum {  // BxDFType, reflection.h:119-127
 };
 
 enum LobeKind { LOBE_LAMBERT, LOBE_OREN_NAYAR, LOBE_MICRO_REFL, LOBE_MICRO_TRANS, LOBE_FRESNEL_SPECULAR, LOBE_SPEC_REFL_NOOP,
-                LOBE_MICRO_REFL_COND /* MicrofacetReflection with FresnelConductor(1, T, K): metal */ };
+                LOBE_MICRO_REFL_COND /* MicrofacetReflection with FresnelConductor(1, T, K): metal */,
+                LOBE_SPEC_REFL_DIEL /* SpecularReflection with FresnelDielectric(etaA, etaB) */,
+                LOBE_SPEC_TRANS /* SpecularTransmission(R, etaA, etaB, Radiance) */ };
 
 struct Lobe {
     int kind;
@@ -39,12 +41,14 @@ struct Lobe {
     float etaA, etaB;  // dielectric Fresnel (etaI, etaT) / transmission indices
 };
 
+constexpr int kMaxLobes = 5;  // UberMaterial adds up to five BxDFs (uber.cpp:45-105)
+
 struct MatLobes {  // what ComputeScatteringFunctions adds for one material (bsdf_eval.h:makeMaterialLobes)
     int nLobes;
     float eta;       // BSDF::eta
     int dispersive;  // eta (and every lobe's etaT) follows the path's wavelength
     int pad;
-    Lobe lobes[2];
+    Lobe lobes[kMaxLobes];
 };
 
 struct BSDF {

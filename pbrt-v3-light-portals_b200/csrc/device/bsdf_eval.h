@@ -135,6 +135,21 @@ PG_HD_NOINLINE Spec lobeSample(const Lobe &l, float etaB, V3 wo, float u0, float
         *pdf = 1 - F;
         return ft / absCosTheta(*wi);
     }
+    case LOBE_SPEC_REFL_DIEL: {  // SpecularReflection::Sample_f with FresnelDielectric, reflection.cpp:131-141
+        *wi = v3(-wo.x, -wo.y, wo.z);
+        *pdf = 1;
+        return frDielectric(cosTheta(*wi), l.etaA, etaB) * l.R / absCosTheta(*wi);
+    }
+    case LOBE_SPEC_TRANS: {  // SpecularTransmission::Sample_f, reflection.cpp:148-163 (TransportMode::Radiance)
+        bool entering = cosTheta(wo) > 0;
+        float etaI = entering ? l.etaA : etaB;
+        float etaT = entering ? etaB : l.etaA;
+        if (!refract(wo, faceforward(v3(0, 0, 1), wo), etaI / etaT, wi)) return spec(0.f);
+        *pdf = 1;
+        Spec ft = l.R * (spec(1.f) - spec(frDielectric(cosTheta(*wi), l.etaA, etaB)));
+        ft *= (etaI * etaI) / (etaT * etaT);
+        return ft / absCosTheta(*wi);
+    }
     default: {  // LOBE_SPEC_REFL_NOOP: SpecularReflection with FresnelNoOp
         *wi = v3(-wo.x, -wo.y, wo.z);
         *pdf = 1;
@@ -314,6 +329,51 @@ PG_HD void makeMaterialLobes(int tag, const float *mp, MatLobes *m) {
         l.R = spec(1.f);
         l.T = loadSpec(mp), l.K = loadSpec(mp + 3);
         l.a = mp[6], l.b = mp[7];
+    } else if (tag == PBRTGPU_MAT_UBER) {  // materials/uber.cpp:45-105
+        Spec Kd = loadSpec(mp), Ks = loadSpec(mp + 3), Kr = loadSpec(mp + 6), Kt = loadSpec(mp + 9), op = loadSpec(mp + 12);
+        float e = mp[17];
+        Spec t = clampSpec(-op + spec(1.f));
+        if (!isBlack(t)) {
+            m->eta = 1.f;
+            Lobe &l = m->lobes[m->nLobes++];
+            l.kind = LOBE_SPEC_TRANS;
+            l.type = BSDF_TRANSMISSION | BSDF_SPECULAR;
+            l.R = t;
+            l.etaA = 1.f, l.etaB = 1.f;
+        } else
+            m->eta = e;
+        Spec kd = op * Kd;
+        if (!isBlack(kd)) {
+            Lobe &l = m->lobes[m->nLobes++];
+            l.kind = LOBE_LAMBERT;
+            l.type = BSDF_REFLECTION | BSDF_DIFFUSE;
+            l.R = kd;
+        }
+        Spec ks = op * Ks;
+        if (!isBlack(ks)) {
+            Lobe &l = m->lobes[m->nLobes++];
+            l.kind = LOBE_MICRO_REFL;
+            l.type = BSDF_REFLECTION | BSDF_GLOSSY;
+            l.R = ks;
+            l.a = mp[15], l.b = mp[16];
+            l.etaA = 1.f, l.etaB = e;
+        }
+        Spec kr = op * Kr;
+        if (!isBlack(kr)) {
+            Lobe &l = m->lobes[m->nLobes++];
+            l.kind = LOBE_SPEC_REFL_DIEL;
+            l.type = BSDF_REFLECTION | BSDF_SPECULAR;
+            l.R = kr;
+            l.etaA = 1.f, l.etaB = e;
+        }
+        Spec kt = op * Kt;
+        if (!isBlack(kt)) {
+            Lobe &l = m->lobes[m->nLobes++];
+            l.kind = LOBE_SPEC_TRANS;
+            l.type = BSDF_TRANSMISSION | BSDF_SPECULAR;
+            l.R = kt;
+            l.etaA = 1.f, l.etaB = e;
+        }
     } else if (tag == PBRTGPU_MAT_MIRROR) {
         Spec R = loadSpec(mp);
         if (!isBlack(R)) {

@@ -25,6 +25,10 @@ PG_HD Spec spec(float v) { return spec(v, v, v); }
 PG_HD Spec loadSpec(const float *p) { return spec(PG_LD(p), PG_LD(p + 1), PG_LD(p + 2)); }
 PG_HD Spec operator+(Spec a, Spec b) { return spec(a.r + b.r, a.g + b.g, a.b + b.b); }
 PG_HD Spec operator-(Spec a, Spec b) { return spec(a.r - b.r, a.g - b.g, a.b - b.b); }
+PG_HD Spec operator-(Spec a) { return spec(-a.r, -a.g, -a.b); }
+PG_HD Spec clampSpec(Spec a) {  // CoefficientSpectrum::Clamp(0, Infinity), spectrum.h:244-251
+    return spec(a.r < 0.f ? 0.f : a.r, a.g < 0.f ? 0.f : a.g, a.b < 0.f ? 0.f : a.b);
+}
 PG_HD Spec operator*(Spec a, Spec b) { return spec(a.r * b.r, a.g * b.g, a.b * b.b); }
 PG_HD Spec operator*(Spec a, float s) { return spec(a.r * s, a.g * s, a.b * s); }
 PG_HD Spec operator*(float s, Spec a) { return spec(a.r * s, a.g * s, a.b * s); }

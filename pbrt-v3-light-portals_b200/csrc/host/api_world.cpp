@@ -131,6 +131,19 @@ int SceneApi::makeMaterial(const std::string &name, const ParamSet &shapeParams,
         float vr = mp.has("vroughness") ? mp.scalar("vroughness", 0.f) : rough;
         if (mp.boolean("remaproughness", true)) ur = roughnessToAlpha(ur), vr = roughnessToAlpha(vr);
         m.params[6] = ur, m.params[7] = vr;
+    } else if (name == "uber") {  // materials/uber.cpp:107-135
+        m.tag = PBRTGPU_MAT_UBER;
+        put3(m.params + 0, mp.spectrum("Kd", RGB(0.25f)).clamp());
+        put3(m.params + 3, mp.spectrum("Ks", RGB(0.25f)).clamp());
+        put3(m.params + 6, mp.spectrum("Kr", RGB(0.f)).clamp());
+        put3(m.params + 9, mp.spectrum("Kt", RGB(0.f)).clamp());
+        put3(m.params + 12, mp.spectrum("opacity", RGB(1.f)).clamp());
+        float rough = mp.scalar("roughness", .1f);
+        float ru = mp.has("uroughness") ? mp.scalar("uroughness", 0.f) : rough;
+        float rv = mp.has("vroughness") ? mp.scalar("vroughness", 0.f) : ru;
+        if (mp.boolean("remaproughness", true)) ru = roughnessToAlpha(ru), rv = roughnessToAlpha(rv);
+        m.params[15] = ru, m.params[16] = rv;
+        m.params[17] = mp.has("eta") ? mp.scalar("eta", 1.5f) : mp.scalar("index", 1.5f);
     } else if (name == "mirror") {  // materials/mirror.cpp:45-64
         m.tag = PBRTGPU_MAT_MIRROR;
         put3(m.params + 0, mp.spectrum("Kr", RGB(0.9f)).clamp());

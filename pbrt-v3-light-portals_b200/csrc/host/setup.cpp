@@ -345,8 +345,10 @@ bool makeRenderSetup(const SceneDesc &d, RenderSetup *out) {
         // With allowMultipleLobes = false (integrator.cpp:615) glass is SpecularReflection + SpecularTransmission,
         // and Li recurses into BOTH (directlighting.cpp:91-95): a tree of rays, not a path.  Not built yet.
         for (auto &m : d.materials)
-            if (m.tag == PBRTGPU_MAT_GLASS || m.tag == PBRTGPU_MAT_DISPERSIVE_GLASS) {
-                hostError("Integrator \"directlighting\": materials with specular transmission (glass, dispersive_glass) are not supported "
+            if (m.tag == PBRTGPU_MAT_GLASS || m.tag == PBRTGPU_MAT_DISPERSIVE_GLASS ||
+                (m.tag == PBRTGPU_MAT_UBER && (m.params[9] != 0 || m.params[10] != 0 || m.params[11] != 0 || m.params[12] < 1 ||
+                                               m.params[13] < 1 || m.params[14] < 1))) {
+                hostError("Integrator \"directlighting\": materials with specular transmission (glass, dispersive_glass, uber with Kt or opacity < 1) are not supported "
                           "by the GPU integrator (its specular recursion follows reflection only)");
                 return false;
             }

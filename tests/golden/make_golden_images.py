@@ -27,6 +27,11 @@ CASES = {
     # Integrator "directlighting": UniformSampleAllLights with sample arrays, and UniformSampleOneLight
     "direct_all": ("direct_mixed.pbrt", {"DIRECT_STRATEGY": "all"}),
     "direct_one": ("direct_mixed.pbrt", {"DIRECT_STRATEGY": "one"}),
+    # Material "uber" with all five BxDFs (specular transmission for opacity, Lambert, microfacet, specular reflection,
+    # specular transmission), under the path integrator
+    "uber_path": ("direct_mixed.pbrt", {'Integrator "directlighting" "integer maxdepth" [3] "string strategy" "DIRECT_STRATEGY"': 'Integrator "path" "integer maxdepth" [6]',
+                                        'Material "plastic" "rgb Kd" [.3 .5 .3] "rgb Ks" [.4 .4 .4] "float roughness" [.1]':
+                                        'Material "uber" "rgb Kd" [.3 .5 .3] "rgb Ks" [.3 .3 .3] "rgb Kr" [.4 .4 .4] "rgb Kt" [.5 .5 .6] "rgb opacity" [.8 .8 .8] "float roughness" [.15] "float index" [1.4]'}),
     # the portal room under directlighting "all" (how the fork's own scenes use portals)
     "portal_room_direct": ("portal_room.pbrt", {"STRATEGY": "portal", 'Integrator "path" "integer maxdepth" [4]': 'Integrator "directlighting"'}),
 }

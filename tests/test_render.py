@@ -250,6 +250,11 @@ ANALYTIC = {
                             'Material "matte" "rgb Kd" [.5 .5 .5] "float sigma" [0]\nReverseOrientation\nShape "sphere" "float radius" [1]\n',
     "sphere_4_point_lights": 'LightSource "point" "rgb I" [0.785398163 0.785398163 0.785398163]\n' * 4 +
                              'Material "matte" "rgb Kd" [.5 .5 .5] "float sigma" [0]\nReverseOrientation\nShape "sphere" "float radius" [1]\n',
+    # analytic_scenes.cpp:166-204: UberMaterial Kd 0.25, Kr 0.5, index 1 (a specular lobe that reflects nothing), I = 3 pi
+    "sphere_uber_point_light": 'LightSource "point" "rgb I" [9.42477796 9.42477796 9.42477796]\n'
+                               'Material "uber" "rgb Kd" [.25 .25 .25] "rgb Ks" [0 0 0] "rgb Kr" [.5 .5 .5] "rgb Kt" [0 0 0] "float roughness" [0] '
+                               '"float uroughness" [0] "float vroughness" [0] "rgb opacity" [1 1 1] "float index" [1] "bool remaproughness" "false"\n'
+                               'ReverseOrientation\nShape "sphere" "float radius" [1]\n',
     "emissive_sphere": 'Material "matte" "rgb Kd" [.5 .5 .5] "float sigma" [0]\nReverseOrientation\n'
                        'AreaLightSource "diffuse" "rgb L" [.5 .5 .5]\nShape "sphere" "float radius" [1]\n',
 }

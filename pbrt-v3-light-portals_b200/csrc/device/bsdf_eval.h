@@ -249,11 +249,13 @@ PG_HD_NOINLINE Spec bsdfSampleF(const BSDF &b, V3 woW, V3 *wiW, float u0, float 
 // Material::ComputeScatteringFunctions for the material table of pbrtgpu.h
 // (allowMultipleLobes = true, TransportMode::Radiance, as path.cpp:107 calls it).
 //
+// allowMultipleLobes: true for the path integrator (path.cpp:107), false for SamplerIntegrator-derived
+// Li's such as directlighting (integrator.cpp:615 default) -- it only matters for specular glass.
 // Textures are constants, so which BxDFs a material adds and with what parameters is the same at
 // every vertex: makeMaterialLobes runs ONCE per material (at upload, on the host) and the kernels
 // read the result from a small table.  Per vertex only the shading frame is built -- and, for
 // dispersive_glass, the index of refraction of the path's hero wavelength.
-PG_HD void makeMaterialLobes(int tag, const float *mp, MatLobes *m) {
+PG_HD void makeMaterialLobes(int tag, const float *mp, bool allowMultipleLobes, MatLobes *m) {
     m->nLobes = 0;
     m->eta = 1;
     m->dispersive = 0;
@@ -297,7 +299,22 @@ PG_HD void makeMaterialLobes(int tag, const float *mp, MatLobes *m) {
         m->eta = eta;
         if (isBlack(R) && isBlack(T)) return;
         bool isSpecular = mp[9] != 0.f;
-        if (isSpecular) {
+        if (isSpecular && !allowMultipleLobes) {  // SamplerIntegrator::Li's ComputeScatteringFunctions (glass.cpp:74-87)
+            if (!isBlack(R)) {
+                Lobe &l = m->lobes[m->nLobes++];
+                l.kind = LOBE_SPEC_REFL_DIEL;
+                l.type = BSDF_REFLECTION | BSDF_SPECULAR;
+                l.R = R;
+                l.etaA = 1.f, l.etaB = eta;
+            }
+            if (!isBlack(T)) {
+                Lobe &l = m->lobes[m->nLobes++];
+                l.kind = LOBE_SPEC_TRANS;
+                l.type = BSDF_TRANSMISSION | BSDF_SPECULAR;
+                l.R = T;
+                l.etaA = 1.f, l.etaB = eta;
+            }
+        } else if (isSpecular) {
             Lobe &l = m->lobes[m->nLobes++];
             l.kind = LOBE_FRESNEL_SPECULAR;
             l.type = BSDF_REFLECTION | BSDF_TRANSMISSION | BSDF_SPECULAR;

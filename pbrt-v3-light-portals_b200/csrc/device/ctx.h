@@ -49,6 +49,8 @@ struct pbrtgpu_ctx {
     double profMs[PBRTGPU_K_COUNT] = {0};
     long long profLaunches[PBRTGPU_K_COUNT] = {0};
     unsigned long long *dTraversalCounts = nullptr;
+    int maxSpecTransLobes = 0;                      // per material, allowMultipleLobes = false: > 0 makes directlighting a tree
+    bool specTransDispersive = false;
     long long sumLightSamples = 0;                  // sum of Light::nSamples (directlighting "all")
     bool hasInfiniteLight = false;
     bool hasNullMaterial = false;                   // some primitive has no material (path.cpp:108-113)

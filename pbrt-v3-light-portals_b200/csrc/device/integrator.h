@@ -44,6 +44,9 @@ struct WaveParams {
     int integrator, directStrategy;  // PBRTGPU_INTEGRATOR_*, PBRTGPU_DIRECT_*
     int nSampleArrays;               // 2D sample arrays the integrator requested (DirectLightingIntegrator::Preprocess)
     int neeCapacity;                 // entries of the shadow / next-event queues (nSlots x light samples per vertex)
+    int directTree;                  // directlighting over materials with specular transmission: Li's recursion is a tree
+    int branchCapacity;              // pending branches a path can hold (= maxdepth)
+    F4 *branch;                      // 3 x float4 per entry, branchCapacity entries per slot: {o, valid} {d, depth} {beta, -}
     // batch geometry: slot -> (pixel, sample number)
     int tilesX;            // sample-bounds tiles per row (16 x 16 tiles as integrator.cpp:533-553)
     int shardIndex, shardCount;
@@ -56,7 +59,8 @@ struct WaveParams {
     F4 *L;                 // rgb = radiance so far, w = hero wavelength (nm)
     F4 *beta;              // rgb = throughput, w = etaScale
     int *flags;            // bits 0-7 bounces, bit 8 specularBounce, bit 9 alive (has a film sample),
-                           // bits 10-25 vertices shaded so far (directlighting: which sample arrays are next)
+                           // bits 10-25 vertices shaded so far (directlighting: which sample arrays are next),
+                           // bits 26-30 pending branches (directlighting over specular transmission)
     float *pFilm;          // 2 per slot
     // queues (position-indexed)
     F4 *rays[2];           // closest-hit rays of the current / next depth, 2 x float4 each

@@ -12,19 +12,63 @@ namespace pg {
 
 // ---- stage 2b: a path ray that escaped.  Environment light on the camera ray
 // or after a specular bounce (path.cpp:91-101), then the path ends (path.cpp:104).
-PG_HD void stageMiss(const WaveParams &w, int cur, int pos) {
+// Integrator "directlighting" over materials with specular transmission: Li recurses into reflection, then
+// transmission (directlighting.cpp:91-95).  The tree is walked depth first, one vertex per wavefront
+// iteration: the path follows the reflection branch and keeps the transmission branch of every vertex on a
+// per-slot stack; when the branch it follows ends (a miss, no specular lobe, the depth limit) the most recent
+// pending branch continues.  Each stack entry also stands for SpecularTransmit's sampler.Get2D()
+// (integrator.cpp:684), which the reference draws after the whole reflection subtree: popping an entry
+// advances the sampler dimension by two whether or not the entry carries a ray.
+PG_HD void popBranch(const WaveParams &w, int depth, int cur, int slot) {
+    int flags = w.flags[slot];
+    int count = (flags >> 26) & 31;
+    if (count == 0) return;
+    int dim = w.dim[slot];
+    F4 *stack = w.branch + 3 * (size_t)slot * w.branchCapacity;
+    F4 a = f4(0, 0, 0, 0), b = a, c = a;
+    bool found = false;
+    while (count > 0 && !found) {
+        --count;
+        if (dim + 1 >= kArrayStartDim && dim < w.hal.arrayEndDim) dim = w.hal.arrayEndDim;  // GlobalSampler::Get2D
+        dim += 2;
+        a = stack[3 * count], b = stack[3 * count + 1], c = stack[3 * count + 2];
+        found = a.w != 0.f;
+    }
+    w.dim[slot] = dim;
+    flags = (flags & ~(31 << 26)) | (count << 26);
+    if (found) {
+        int bounces = (int)b.w;
+        flags = (flags & ~0xff) | bounces | 256;
+        F4 bq = w.beta[slot];
+        w.beta[slot] = f4(c.x, c.y, c.z, bq.w);
+        Ray r;
+        r.o = v3(a.x, a.y, a.z), r.d = v3(b.x, b.y, b.z), r.tMax = kInfinity;
+        int np = atomicIncInt(&w.cnt->nActive[depth + 1]);
+        storeRay(w.rays[cur ^ 1], np, r);
+        w.qSlot[cur ^ 1][np] = slot;
+    }
+    w.flags[slot] = flags;
+}
+
+PG_HD void stageMiss(const WaveParams &w, int depth, int cur, int pos) {
     int slot = w.qSlot[cur][pos];
     int flags = w.flags[slot];
     int bounces = flags & 255;
     bool specularBounce = (flags >> 8) & 1;
-    if (!(bounces == 0 || specularBounce)) return;
-    Ray ray = loadRay(w.rays[cur], pos);
-    F4 Lq = w.L[slot], bq = w.beta[slot];
-    Spec L = spec(Lq.x, Lq.y, Lq.z), beta = spec(bq.x, bq.y, bq.z);
-    for (int i = 0; i < w.sc.nLights; ++i)
-        if (PG_LD(w.sc.lightTag + i) == PBRTGPU_LIGHT_INFINITE)
-            L += beta * infiniteLe(w.sc.lightParams + PBRTGPU_LIGHT_STRIDE * (size_t)i, ray.d);
-    w.L[slot] = f4(L.r, L.g, L.b, Lq.w);
+    if (bounces == 0 || specularBounce) {
+        bool any = false;
+        for (int i = 0; i < w.sc.nLights; ++i) any |= PG_LD(w.sc.lightTag + i) == PBRTGPU_LIGHT_INFINITE;
+        if (any) {
+            Ray ray = loadRay(w.rays[cur], pos);
+            F4 Lq = w.L[slot], bq = w.beta[slot];
+            Spec L = spec(Lq.x, Lq.y, Lq.z), beta = spec(bq.x, bq.y, bq.z);
+            for (int i = 0; i < w.sc.nLights; ++i)
+                if (PG_LD(w.sc.lightTag + i) == PBRTGPU_LIGHT_INFINITE)
+                    L += beta * infiniteLe(w.sc.lightParams + PBRTGPU_LIGHT_STRIDE * (size_t)i, ray.d);
+            w.L[slot] = f4(L.r, L.g, L.b, Lq.w);
+        }
+    }
+    if (w.directTree) popBranch(w, depth, cur, slot);
 }
 
 // ---- stage 3: one path vertex (the body of path.cpp:81-187 after scene.Intersect found a hit).
@@ -288,7 +332,7 @@ PG_HD void stageShadeDirect(const WaveParams &w, int depth, int cur, int pos) {
         smp.index = w.hIndex[slot];
         smp.dim = w.dim[slot];
         BSDF bsdf;
-        makeBSDF(it, w.sc.matLobes, mat, w.sc.matParams + PBRTGPU_MAT_STRIDE * (size_t)mat, wvl0, &bsdf);
+        makeBSDF(it, w.sc.matLobes + w.sc.nMaterials, mat, w.sc.matParams + PBRTGPU_MAT_STRIDE * (size_t)mat, wvl0, &bsdf);  // allowMultipleLobes = false
         L += beta * hitLe(w.sc, prim, it.n, -ray.d);
         const int nLights = w.sc.nLights;
         if (nLights > 0) {
@@ -335,19 +379,53 @@ PG_HD void stageShadeDirect(const WaveParams &w, int depth, int cur, int pos) {
                 }
             }
         }
+        int branches = (flags >> 26) & 31;
         if (bounces + 1 < w.maxDepth) {
             V3 wo = -ray.d, wi = v3(0, 0, 0);
             float pdf, u0, u1;
             int sampled;
             get2D(w.hal, smp, &u0, &u1);
             Spec f = bsdfSampleF(bsdf, wo, &wi, u0, u1, &pdf, BSDF_REFLECTION | BSDF_SPECULAR, &sampled);
-            if (pdf > 0.f && !isBlack(f) && absDot(wi, it.ns) != 0.f) {
+            const bool reflects = pdf > 0.f && !isBlack(f) && absDot(wi, it.ns) != 0.f;
+            if (w.directTree) {
+                // SpecularTransmit (integrator.cpp:677-755).  One specular-transmission lobe per material (checked at
+                // setup), so its Sample_f does not depend on the sample it is given.
+                V3 wiT = v3(0, 0, 0);
+                float pdfT, uT0 = 0.5f, uT1 = 0.5f;
+                int sampledT;
+                if (!reflects) get2D(w.hal, smp, &uT0, &uT1);  // no reflection subtree in between: drawn right away
+                Spec fT = bsdfSampleF(bsdf, wo, &wiT, uT0, uT1, &pdfT, BSDF_TRANSMISSION | BSDF_SPECULAR, &sampledT);
+                const bool transmits = pdfT > 0.f && !isBlack(fT) && absDot(wiT, it.ns) != 0.f;
+                if (reflects) {
+                    if (branches < w.branchCapacity) {
+                        F4 *e = w.branch + 3 * ((size_t)slot * w.branchCapacity + branches);
+                        Ray rt;
+                        rt.o = rt.d = v3(0, 0, 0);
+                        Spec bt = spec(0.f);
+                        if (transmits) {
+                            rt = spawnRay(it.p, it.pError, it.n, wiT);
+                            bt = beta * (fT * absDot(wiT, it.ns) / pdfT);
+                        }
+                        e[0] = f4(rt.o.x, rt.o.y, rt.o.z, transmits ? 1.f : 0.f);
+                        e[1] = f4(rt.d.x, rt.d.y, rt.d.z, (float)(bounces + 1));
+                        e[2] = f4(bt.r, bt.g, bt.b, 0.f);
+                        ++branches;
+                    }
+                } else if (transmits) {
+                    beta *= fT * absDot(wiT, it.ns) / pdfT;
+                    next = spawnRay(it.p, it.pError, it.n, wiT);
+                    ++bounces;
+                    alive = true;
+                }
+            }
+            if (reflects) {
                 beta *= f * absDot(wi, it.ns) / pdf;
                 next = spawnRay(it.p, it.pError, it.n, wi);
                 ++bounces;
                 alive = true;
             }
         }
+        flags = (flags & ~(31 << 26)) | (branches << 26);
         w.dim[slot] = smp.dim;
     }
     w.L[slot] = f4(L.r, L.g, L.b, wvl0);
@@ -358,6 +436,9 @@ PG_HD void stageShadeDirect(const WaveParams &w, int depth, int cur, int pos) {
         int np = atomicIncInt(&w.cnt->nActive[depth + 1]);
         storeRay(w.rays[cur ^ 1], np, next);
         w.qSlot[cur ^ 1][np] = slot;
+    } else if (w.directTree) {
+        w.flags[slot] = (flags & ~0x3fffc00) | (((vertices + (mat >= 0 ? 1 : 0)) & 0xffff) << 10);
+        popBranch(w, depth, cur, slot);
     }
 }
 

@@ -155,11 +155,32 @@ inline void finishInfiniteLight(float *lp) {
 }
 
 
-// The per-material BxDF table (bsdf_eval.h:makeMaterialLobes), one entry per material.
+// The per-material BxDF table (bsdf_eval.h:makeMaterialLobes): entries [0, n) with allowMultipleLobes = true
+// (path integrator), entries [n, 2n) with false (directlighting).
 inline void buildMaterialLobes(const pbrtgpu_scene *s, std::vector<MatLobes> *out) {
-    out->resize(s->n_materials > 0 ? s->n_materials : 1);
+    const int n = s->n_materials;
+    out->resize(n > 0 ? 2 * n : 2);
     memset(out->data(), 0, out->size() * sizeof(MatLobes));
-    for (int i = 0; i < s->n_materials; ++i) makeMaterialLobes(s->mat_tag[i], s->mat_params + (size_t)i * PBRTGPU_MAT_STRIDE, &(*out)[i]);
+    for (int i = 0; i < n; ++i) {
+        const float *mp = s->mat_params + (size_t)i * PBRTGPU_MAT_STRIDE;
+        makeMaterialLobes(s->mat_tag[i], mp, true, &(*out)[i]);
+        makeMaterialLobes(s->mat_tag[i], mp, false, &(*out)[n + i]);
+    }
+}
+// Specular-transmission lobes per material under allowMultipleLobes = false: 0 everywhere = directlighting's
+// recursion is a path; otherwise it is a tree (SpecularReflect + SpecularTransmit, directlighting.cpp:91-95).
+inline int maxSpecularTransmissionLobes(const std::vector<MatLobes> &table, int nMaterials, bool *dispersive) {
+    int worst = 0;
+    *dispersive = false;
+    for (int i = 0; i < nMaterials; ++i) {
+        const MatLobes &m = table[nMaterials + i];
+        int c = 0;
+        for (int k = 0; k < m.nLobes; ++k)
+            if ((m.lobes[k].type & (BSDF_TRANSMISSION | BSDF_SPECULAR)) == (BSDF_TRANSMISSION | BSDF_SPECULAR)) ++c;
+        if (c > 0 && m.dispersive) *dispersive = true;
+        worst = c > worst ? c : worst;
+    }
+    return worst;
 }
 
 // PathIntegrator::Preprocess -> CreateLightSampleDistribution (core/lightdistrib.cpp:48-66,

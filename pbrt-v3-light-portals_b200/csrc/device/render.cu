@@ -198,11 +198,11 @@ __global__ void __launch_bounds__(512, 1) k_shade_direct(WaveParams w, int depth
     }
 }
 
-// escaped rays: only launched when the scene has an infinite light
+// escaped rays: only launched when the scene has an infinite light or paths keep pending branches (directlighting tree mode)
 __global__ void __launch_bounds__(kStageBlock) k_miss(WaveParams w, int depth, int cur) {
     int n = w.cnt->nMiss[depth];
     int stride = gridDim.x * blockDim.x;
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) stageMiss(w, cur, w.missIdx[i]);
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) stageMiss(w, depth, cur, w.missIdx[i]);
 }
 
 template <bool COUNT>
@@ -238,23 +238,27 @@ __global__ void __launch_bounds__(kStageBlock) k_film(WaveParams w) {
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < w.nSlots; i += stride) stageFilm(w, i);
 }
 
-// fold one batch's counters into the running totals, then clear them for the next batch
-__global__ void k_batch_stats(WaveCounters *cnt, unsigned long long *totals, int depths) {
+// fold one batch's counters into the running totals, then clear them for the next batch.
+// carry != 0 (directlighting tree mode, paths still hold pending branches after `depths` iterations): the
+// queue of depth `depths` becomes the queue of depth 0 of another round of iterations over the same batch.
+__global__ void k_batch_stats(WaveCounters *cnt, unsigned long long *totals, int depths, int carry, int firstRound) {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
     unsigned long long closest = 0, shadow = 0, nee = 0, culled = 0;
-    for (int d = 0; d <= depths; ++d) closest += (unsigned long long)cnt->nActive[d];
+    for (int d = 0; d < depths + (carry ? 0 : 1); ++d) closest += (unsigned long long)cnt->nActive[d];
     for (int d = 0; d < depths; ++d)
         nee += (unsigned long long)cnt->nNee[d], shadow += (unsigned long long)cnt->nShadow[d], culled += (unsigned long long)cnt->nNeeCulled[d];
     totals[5] += culled;
-    totals[0] += (unsigned long long)cnt->nActive[0];
+    if (firstRound) totals[0] += (unsigned long long)cnt->nActive[0];
     totals[1] += closest + nee;
     totals[4] += nee;
     totals[2] += shadow;
     totals[3] += cnt->scrubbed;
+    const int a = cnt->nActive[depths], h = depths < kMaxDepthSlots ? cnt->nHit[depths] : 0, m = depths < kMaxDepthSlots ? cnt->nMiss[depths] : 0;
     for (int d = 0; d <= kMaxDepthSlots; ++d) cnt->nActive[d] = 0;
     for (int d = 0; d < kMaxDepthSlots; ++d)
         cnt->nShadow[d] = cnt->nNee[d] = cnt->nHit[d] = cnt->nMiss[d] = cnt->fetch[0][d] = cnt->fetch[1][d] = cnt->fetch[2][d] = cnt->nNeeCulled[d] = 0;
     cnt->scrubbed = 0;
+    if (carry) cnt->nActive[0] = a, cnt->nHit[0] = h, cnt->nMiss[0] = m;
 }
 
 // Film::MergeFilmTile's RGB -> XYZ (film.cpp:125-127), once per pixel at the end

@@ -182,6 +182,7 @@ int pbrtgpu_upload_scene(pbrtgpu_ctx *ctx, const pbrtgpu_scene *s) {
         std::vector<MatLobes> lobes;
         buildMaterialLobes(s, &lobes);
         UP(lobes.data(), lobes.size(), &d.matLobes);
+        ctx->maxSpecTransLobes = maxSpecularTransmissionLobes(lobes, s->n_materials, &ctx->specTransDispersive);
     }
     UP(s->light_portal_begin, s->light_portal_begin ? s->n_lights + 1 : 0, &d.lightPortalBegin);
     UP(s->light_nsamples, s->light_nsamples ? s->n_lights : 0, &d.lightNSamples);

@@ -31,6 +31,8 @@ inline void fillWaveParams(const pbrtgpu_render_params *rp, WaveParams *w) {
     w->rrThreshold = rp->rr_threshold;
     w->integrator = rp->integrator;
     w->directStrategy = rp->direct_strategy;
+    w->directTree = 0;
+    w->branchCapacity = 0;
     int sw = rp->sample_bounds[2] - rp->sample_bounds[0];
     w->tilesX = (sw + 15) / 16;
     w->shardIndex = rp->shard_index;
@@ -44,6 +46,7 @@ struct BatchPlan {
     int tilesPerBatch;
     int maxSlots;
     int depthIters;      // wavefront iterations per batch
+    int branchPerSlot;   // directlighting tree mode: pending-branch entries per path slot (0 otherwise)
     int neeMult;         // light samples per vertex: the shadow / next-event queues hold maxSlots * neeMult entries
 };
 
@@ -61,9 +64,12 @@ inline int sampleArrayCount(const pbrtgpu_render_params *rp, int nLights) {
     return 2 * nLights * (rp->max_depth > 0 ? rp->max_depth : 0);
 }
 
-inline BatchPlan planBatches(const pbrtgpu_render_params *rp, long long targetSlots, bool hasNullMaterial, int neeMult = 1) {
+inline BatchPlan planBatches(const pbrtgpu_render_params *rp, long long targetSlots, bool hasNullMaterial, int neeMult = 1,
+                             int branchPerSlot = 0) {
     BatchPlan p;
     targetSlots /= neeMult;
+    targetSlots = targetSlots * 290 / (290 + 48LL * branchPerSlot);  // keep the batch's memory roughly constant
+    p.branchPerSlot = branchPerSlot;
     int sw = rp->sample_bounds[2] - rp->sample_bounds[0], sh = rp->sample_bounds[3] - rp->sample_bounds[1];
     p.tilesX = (sw + 15) / 16;
     p.tilesY = (sh + 15) / 16;
@@ -85,6 +91,8 @@ inline BatchPlan planBatches(const pbrtgpu_render_params *rp, long long targetSl
     p.neeMult = neeMult;
     p.depthIters = rp->max_depth + 1 + (hasNullMaterial ? 8 : 0);
     if (rp->integrator == PBRTGPU_INTEGRATOR_DIRECT) p.depthIters = (rp->max_depth > 1 ? rp->max_depth : 1) + (hasNullMaterial ? 8 : 0);
+    // tree mode: a path walks up to 2^maxdepth - 1 vertices, one per wavefront iteration
+    if (branchPerSlot > 0) p.depthIters = (rp->max_depth < 6 ? (1 << rp->max_depth) : 64) + (hasNullMaterial ? 8 : 0);
     if (p.depthIters > kMaxDepthSlots - 1) p.depthIters = kMaxDepthSlots - 1;  // stage d touches the counters of depth d + 1
     return p;
 }
@@ -92,10 +100,10 @@ inline BatchPlan planBatches(const pbrtgpu_render_params *rp, long long targetSl
 // Bytes per slot of each wave buffer, in the order render.cu / hostsim bind them.
 enum WaveBuf {
     WB_HINDEX, WB_DIM, WB_L, WB_BETA, WB_FLAGS, WB_PFILM, WB_RAYS0, WB_RAYS1, WB_Q0, WB_Q1, WB_HITS, WB_SHADOW_RAYS,
-    WB_SHADOW_CONTRIB, WB_NEE_RAYS, WB_NEE_CONTRIB, WB_NEE_INFO, WB_NEE_HITS, WB_SHADOW_OCC, WB_HIT_IDX, WB_MISS_IDX, WB_COUNT
+    WB_SHADOW_CONTRIB, WB_NEE_RAYS, WB_NEE_CONTRIB, WB_NEE_INFO, WB_NEE_HITS, WB_SHADOW_OCC, WB_HIT_IDX, WB_MISS_IDX, WB_BRANCH, WB_COUNT
 };
 inline size_t waveBufBytesPerSlot(int b) {
-    static const size_t sz[WB_COUNT] = {8, 4, 16, 16, 4, 8, 32, 32, 4, 4, 16, 32, 16, 32, 16, 8, 16, 1, 4, 4};
+    static const size_t sz[WB_COUNT] = {8, 4, 16, 16, 4, 8, 32, 32, 4, 4, 16, 32, 16, 32, 16, 8, 16, 1, 4, 4, 48};
     return sz[b];
 }
 inline bool waveBufIsLightSampleQueue(int b) {
@@ -103,6 +111,7 @@ inline bool waveBufIsLightSampleQueue(int b) {
            b == WB_SHADOW_OCC;
 }
 inline size_t waveBufBytes(int b, const BatchPlan &p) {
+    if (b == WB_BRANCH) return waveBufBytesPerSlot(b) * (size_t)p.maxSlots * (size_t)p.branchPerSlot + 48;
     return waveBufBytesPerSlot(b) * (size_t)p.maxSlots * (waveBufIsLightSampleQueue(b) ? (size_t)p.neeMult : 1);
 }
 inline void bindWaveBuffers(WaveParams *w, void *const bufs[WB_COUNT]) {
@@ -126,6 +135,7 @@ inline void bindWaveBuffers(WaveParams *w, void *const bufs[WB_COUNT]) {
     w->shadowOcc = (unsigned char *)bufs[WB_SHADOW_OCC];
     w->hitIdx = (int *)bufs[WB_HIT_IDX];
     w->missIdx = (int *)bufs[WB_MISS_IDX];
+    w->branch = (F4 *)bufs[WB_BRANCH];
 }
 
 }  // namespace pg

@@ -342,16 +342,20 @@ bool makeRenderSetup(const SceneDesc &d, RenderSetup *out) {
     if (d.integratorName == "directlighting") {
         // CreateDirectLightingIntegrator, directlighting.cpp:100-137
         rp.integrator = PBRTGPU_INTEGRATOR_DIRECT;
-        // With allowMultipleLobes = false (integrator.cpp:615) glass is SpecularReflection + SpecularTransmission,
-        // and Li recurses into BOTH (directlighting.cpp:91-95): a tree of rays, not a path.  Not built yet.
-        for (auto &m : d.materials)
-            if (m.tag == PBRTGPU_MAT_GLASS || m.tag == PBRTGPU_MAT_DISPERSIVE_GLASS ||
-                (m.tag == PBRTGPU_MAT_UBER && (m.params[9] != 0 || m.params[10] != 0 || m.params[11] != 0 || m.params[12] < 1 ||
-                                               m.params[13] < 1 || m.params[14] < 1))) {
-                hostError("Integrator \"directlighting\": materials with specular transmission (glass, dispersive_glass, uber with Kt or opacity < 1) are not supported "
-                          "by the GPU integrator (its specular recursion follows reflection only)");
+        // With allowMultipleLobes = false (integrator.cpp:615) glass is SpecularReflection + SpecularTransmission and
+        // Li recurses into BOTH (directlighting.cpp:91-95).  The device walks that tree depth first with a per-path
+        // branch stack (integrator_stages.h); it evaluates the transmission branch when it is pushed, which is only
+        // the reference's result if the sample drawn later cannot change it -- i.e. one specular-transmission lobe.
+        for (auto &m : d.materials) {
+            bool twoTransLobes = m.tag == PBRTGPU_MAT_UBER && (m.params[9] != 0 || m.params[10] != 0 || m.params[11] != 0) &&
+                                 (m.params[12] < 1 || m.params[13] < 1 || m.params[14] < 1);
+            if (m.tag == PBRTGPU_MAT_DISPERSIVE_GLASS || twoTransLobes) {
+                hostError("Integrator \"directlighting\": %s is not supported by the GPU integrator",
+                          twoTransLobes ? "Material \"uber\" with both Kt and opacity < 1 (two specular transmission lobes)"
+                                        : "Material \"dispersive_glass\"");
                 return false;
             }
+        }
         std::string st = ip.findOneString("strategy", "all");
         if (st == "one") rp.direct_strategy = PBRTGPU_DIRECT_ONE;
         else if (st == "all") rp.direct_strategy = PBRTGPU_DIRECT_ALL;

@@ -34,6 +34,9 @@ CASES = {
                                         'Material "uber" "rgb Kd" [.3 .5 .3] "rgb Ks" [.3 .3 .3] "rgb Kr" [.4 .4 .4] "rgb Kt" [.5 .5 .6] "rgb opacity" [.8 .8 .8] "float roughness" [.15] "float index" [1.4]'}),
     # the portal room under directlighting "all" (how the fork's own scenes use portals)
     "portal_room_direct": ("portal_room.pbrt", {"STRATEGY": "portal", 'Integrator "path" "integer maxdepth" [4]': 'Integrator "directlighting"'}),
+    # directlighting over glass and uber with Kt: Li recurses into reflection AND transmission (directlighting.cpp:91-95)
+    "direct_glass_all": ("direct_glass.pbrt", {}),
+    "direct_glass_one": ("direct_glass.pbrt", {'"integer maxdepth" [5] "string strategy" "all"': '"integer maxdepth" [7] "string strategy" "one"'}),
 }
 
 

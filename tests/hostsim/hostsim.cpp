@@ -132,7 +132,14 @@ extern "C" int hostsim_render(void *p, const pbrtgpu_render_params *rp, float *f
     w.sc = sc;
     std::vector<unsigned long long> magic = primeMagics(primes);
     w.hal.primes = primes.data(), w.hal.primeSums = sums.data(), w.hal.perms = perms.data(), w.hal.primeMagic = magic.data();
-    BatchPlan pl = planBatches(rp, 1 << 18, nullMat, lightSamplesPerVertex(rp, s));
+    bool dispersiveTrans = false;
+    const bool tree = rp->integrator == PBRTGPU_INTEGRATOR_DIRECT && rp->max_depth > 1 &&
+                      maxSpecularTransmissionLobes(matLobes, s->n_materials, &dispersiveTrans) > 0;
+    BatchPlan pl = planBatches(rp, 1 << 18, nullMat, lightSamplesPerVertex(rp, s), tree ? rp->max_depth : 0);
+    w.directTree = tree ? 1 : 0;
+    w.branchCapacity = tree ? rp->max_depth : 0;
+    if (const char *e = getenv("PBRTGPU_TREE_ROUND_ITERS"))  // tests: short rounds, so that the carry between rounds is exercised
+        if (tree && atoi(e) > 0 && atoi(e) < pl.depthIters) pl.depthIters = atoi(e);
     w.nSampleArrays = sampleArrayCount(rp, s->n_lights);
     w.hal.arrayEndDim = kArrayStartDim + 2 * w.nSampleArrays;
     const int *cb = rp->cropped_bounds;
@@ -161,6 +168,8 @@ extern "C" int hostsim_render(void *p, const pbrtgpu_render_params *rp, float *f
             memset(&cnt, 0, sizeof(cnt));
             parallelFor(w.nSlots, threads, [&](int64_t a, int64_t b) { for (int64_t i = a; i < b; ++i) stageRaygen(w, (int)i); });
             int cur = 0;
+            bool firstRound = true;
+            for (bool again = true; again;) {
             for (int d = 0; d < pl.depthIters; ++d) {
                 int n = cnt.nActive[d];
                 parallelFor(n, threads, [&](int64_t a, int64_t b) {
@@ -175,7 +184,7 @@ extern "C" int hostsim_render(void *p, const pbrtgpu_render_params *rp, float *f
                             w.missIdx[atomicIncInt(&cnt.nMiss[d])] = (int)i;
                     }
                 });
-                parallelFor(cnt.nMiss[d], threads, [&](int64_t a, int64_t b) { for (int64_t i = a; i < b; ++i) stageMiss(w, cur, w.missIdx[i]); });
+                parallelFor(cnt.nMiss[d], threads, [&](int64_t a, int64_t b) { for (int64_t i = a; i < b; ++i) stageMiss(w, d, cur, w.missIdx[i]); });
                 parallelFor(cnt.nHit[d], threads, [&](int64_t a, int64_t b) { 
                     for (int64_t i = a; i < b; ++i) {
                         if (w.integrator == PBRTGPU_INTEGRATOR_DIRECT) stageShadeDirect(w, d, cur, w.hitIdx[i]);
@@ -201,8 +210,15 @@ extern "C" int hostsim_render(void *p, const pbrtgpu_render_params *rp, float *f
                 totals[2] += cnt.nShadow[d];
                 cur ^= 1;
             }
+            // tree mode: paths that still hold pending branches go through another round (render_host.inc, anotherRound)
+            if (firstRound) totals[0] += cnt.nActive[0];
+            firstRound = false;
+            int left = cnt.nActive[pl.depthIters];
+            again = w.directTree && left > 0;
+            memset(&cnt, 0, sizeof(cnt));
+            cnt.nActive[0] = again ? left : 0;
+            }
             parallelFor(w.nSlots, threads, [&](int64_t a, int64_t b) { for (int64_t i = a; i < b; ++i) stageFilm(w, (int)i); });
-            totals[0] += cnt.nActive[0];
             totals[3] += (int64_t)cnt.scrubbed;
         }
     }

@@ -114,13 +114,31 @@ def test_reference_scenes_against_live_reference(pkg, hostsim_lib, name, kw, tmp
     assert s["rel_rmse"] <= CPU_TOL, s
 
 
-def test_directlighting_refuses_specular_transmission(pkg):
-    """DirectLightingIntegrator::Li recurses into reflection AND transmission (directlighting.cpp:91-95): a tree.
-    The GPU integrator follows reflection only and says so instead of rendering something else."""
+def test_directlighting_refuses_what_the_tree_walk_cannot_reproduce(pkg):
+    """DirectLightingIntegrator::Li recurses into reflection AND transmission (directlighting.cpp:91-95).  The device
+    walks that tree with a branch stack and evaluates the transmission branch before the reference draws its sample;
+    materials for which that sample matters (dispersive_glass, uber with Kt and opacity < 1) are refused at load."""
     text = scene_text("box_glass").replace('Integrator "path"', 'Integrator "directlighting"')
-    assert 'Integrator "directlighting"' in text
+    assert 'Integrator "directlighting"' in text and "dispersive_glass" in text
     with pytest.raises(pkg.PbrtGpuError):
         pkg.HostScene(text=text, base_dir=os.path.join(ROOT, "tests", "scenes"))
+    text = scene_text("direct_glass_all").replace('"rgb Kt" [0.5 0.6 0.5]', '"rgb Kt" [0.5 0.6 0.5] "rgb opacity" [0.5 0.5 0.5]')
+    assert "opacity" in text
+    with pytest.raises(pkg.PbrtGpuError):
+        pkg.HostScene(text=text, base_dir=os.path.join(ROOT, "tests", "scenes"))
+
+
+def test_directlighting_tree_rounds_carry_pending_branches(pkg, hostsim_lib, golden, monkeypatch):
+    """Paths that still hold pending transmission branches after a round of iterations continue in another round
+    (render_host.inc, anotherRound; hostsim mirrors it): three iterations per round must give the same image."""
+    monkeypatch.setenv("PBRTGPU_TREE_ROUND_ITERS", "3")
+    hs = load_case(pkg, "direct_glass_one")
+    rgb, _, st = util.hostsim_render(hostsim_lib, hs)
+    s = util.image_stats(rgb, golden["direct_glass_one"])
+    assert s["rel_rmse"] <= CPU_TOL, s
+    monkeypatch.delenv("PBRTGPU_TREE_ROUND_ITERS")
+    _, _, st_one_round = util.hostsim_render(hostsim_lib, hs)
+    assert list(st) == list(st_one_round)  # the same rays, counted once
 
 
 def test_halton_first_dimensions_known_answers(pkg, hostsim_lib):
@@ -164,6 +182,22 @@ def test_gpu_matches_reference_image(pkg, gpu, golden, case):
     sb = hs.params.sample_bounds
     assert stats.camera_rays == (sb[2] - sb[0]) * (sb[3] - sb[1]) * hs.params.spp
     assert stats.scrubbed == 0 and stats.kernel_launches > 0
+
+
+@pytest.mark.gpu
+def test_gpu_directlighting_tree_rounds(pkg, gpu, golden, monkeypatch):
+    """Rounds of three iterations (pending branches carried from one round to the next) give the same
+    image and the same ray counts as one long round."""
+    hs = load_case(pkg, "direct_glass_one")
+    gpu.upload(hs)
+    _, whole = gpu.render(hs.params)
+    monkeypatch.setenv("PBRTGPU_TREE_ROUND_ITERS", "3")
+    film, stats = gpu.render(hs.params)
+    s = util.image_stats(hs.film_to_rgb(film), golden["direct_glass_one"])
+    for k, tol in GPU_TOL.items():
+        assert s[k] <= tol, s
+    assert (stats.camera_rays, stats.closest_rays, stats.shadow_rays) == (whole.camera_rays, whole.closest_rays, whole.shadow_rays)
+    assert stats.kernel_launches > whole.kernel_launches
 
 
 @pytest.mark.gpu

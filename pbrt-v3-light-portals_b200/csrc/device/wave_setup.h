@@ -91,8 +91,9 @@ inline BatchPlan planBatches(const pbrtgpu_render_params *rp, long long targetSl
     p.neeMult = neeMult;
     p.depthIters = rp->max_depth + 1 + (hasNullMaterial ? 8 : 0);
     if (rp->integrator == PBRTGPU_INTEGRATOR_DIRECT) p.depthIters = (rp->max_depth > 1 ? rp->max_depth : 1) + (hasNullMaterial ? 8 : 0);
-    // tree mode: a path walks up to 2^maxdepth - 1 vertices, one per wavefront iteration
-    if (branchPerSlot > 0) p.depthIters = (rp->max_depth < 6 ? (1 << rp->max_depth) : 64) + (hasNullMaterial ? 8 : 0);
+    // tree mode: a path walks up to 2^maxdepth - 1 vertices, one per wavefront iteration.  The iterations run in
+    // rounds of this many; after each round the host looks whether any path is left (render_host.inc, anotherRound)
+    if (branchPerSlot > 0) p.depthIters = 2 * rp->max_depth + 2 + (hasNullMaterial ? 8 : 0);
     if (p.depthIters > kMaxDepthSlots - 1) p.depthIters = kMaxDepthSlots - 1;  // stage d touches the counters of depth d + 1
     return p;
 }

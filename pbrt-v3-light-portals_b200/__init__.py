@@ -132,7 +132,7 @@ def gpu_lib():
     """Load libpbrtgpu.so.  Loading needs libcudart but no device."""
     global _gpu
     if _gpu is None:
-        path = os.path.join(_LIB, "libpbrtgpu.so")
+        path = os.environ.get("PBRTGPU_LIBRARY") or os.path.join(_LIB, "libpbrtgpu.so")  # the override is for A/B builds (tools/build_variants.py)
         if not os.path.exists(path):
             raise PbrtGpuError("libpbrtgpu.so is not built; run __graft_entry__.build() (there is no CPU fallback)")
         lib = C.CDLL(path)

@@ -23,6 +23,23 @@
 #define PG_HD_NOINLINE inline
 #endif
 
+// Call boundaries of the shade stage, by group (tuning: -DPG_NI_BSDF=PG_HD inlines that group)
+#ifndef PG_NI_INTERACTION
+#define PG_NI_INTERACTION PG_HD_NOINLINE
+#endif
+#ifndef PG_NI_SAMPLER
+#define PG_NI_SAMPLER PG_HD_NOINLINE
+#endif
+#ifndef PG_NI_LOBE
+#define PG_NI_LOBE PG_HD_NOINLINE
+#endif
+#ifndef PG_NI_BSDF
+#define PG_NI_BSDF PG_HD_NOINLINE
+#endif
+#ifndef PG_NI_DIRECT
+#define PG_NI_DIRECT PG_HD_NOINLINE
+#endif
+
 // read-only global loads (scalar); on the host a plain dereference
 #if defined(__CUDA_ARCH__)
 #define PG_LD(p) __ldg(p)

@@ -63,7 +63,7 @@ PG_HD Spec orenNayarF(const Lobe &l, V3 wo, V3 wi) {
     return l.R * kInvPi * (l.a + l.b * maxCos * sinAlpha * tanBeta);
 }
 
-PG_HD_NOINLINE Spec lobeF(const Lobe &l, float etaB, V3 wo, V3 wi) {
+PG_NI_LOBE Spec lobeF(const Lobe &l, float etaB, V3 wo, V3 wi) {
     switch (l.kind) {
     case LOBE_LAMBERT: return l.R * kInvPi;
     case LOBE_OREN_NAYAR: return orenNayarF(l, wo, wi);
@@ -74,7 +74,7 @@ PG_HD_NOINLINE Spec lobeF(const Lobe &l, float etaB, V3 wo, V3 wi) {
     }
 }
 
-PG_HD_NOINLINE float lobePdf(const Lobe &l, float etaB, V3 wo, V3 wi) {
+PG_NI_LOBE float lobePdf(const Lobe &l, float etaB, V3 wo, V3 wi) {
     switch (l.kind) {
     case LOBE_LAMBERT:
     case LOBE_OREN_NAYAR: return sameHemisphere(wo, wi) ? absCosTheta(wi) * kInvPi : 0;
@@ -90,7 +90,7 @@ PG_HD_NOINLINE float lobePdf(const Lobe &l, float etaB, V3 wo, V3 wi) {
 }
 
 // BxDF::Sample_f of each lobe; *pdf must be 0 on entry (BSDF::Sample_f sets it).
-PG_HD_NOINLINE Spec lobeSample(const Lobe &l, float etaB, V3 wo, float u0, float u1, V3 *wi, float *pdf, int *sampledType) {
+PG_NI_LOBE Spec lobeSample(const Lobe &l, float etaB, V3 wo, float u0, float u1, V3 *wi, float *pdf, int *sampledType) {
     switch (l.kind) {
     case LOBE_LAMBERT:
     case LOBE_OREN_NAYAR:
@@ -172,7 +172,7 @@ PG_HD int bsdfNumComponents(const BSDF &b, int flags) {
     return n;
 }
 
-PG_HD_NOINLINE Spec bsdfF(const BSDF &b, V3 woW, V3 wiW, int flags) {
+PG_NI_BSDF Spec bsdfF(const BSDF &b, V3 woW, V3 wiW, int flags) {
     V3 wi = bsdfWorldToLocal(b, wiW), wo = bsdfWorldToLocal(b, woW);
     if (wo.z == 0) return spec(0.f);
     bool reflect = dot(wiW, b.ng) * dot(woW, b.ng) > 0;
@@ -184,7 +184,7 @@ PG_HD_NOINLINE Spec bsdfF(const BSDF &b, V3 woW, V3 wiW, int flags) {
     return f;
 }
 
-PG_HD_NOINLINE float bsdfPdf(const BSDF &b, V3 woW, V3 wiW, int flags) {
+PG_NI_BSDF float bsdfPdf(const BSDF &b, V3 woW, V3 wiW, int flags) {
     if (b.nLobes == 0) return 0.f;
     V3 wo = bsdfWorldToLocal(b, woW), wi = bsdfWorldToLocal(b, wiW);
     if (wo.z == 0) return 0.f;
@@ -198,7 +198,7 @@ PG_HD_NOINLINE float bsdfPdf(const BSDF &b, V3 woW, V3 wiW, int flags) {
     return matchingComps > 0 ? pdf / matchingComps : 0.f;
 }
 
-PG_HD_NOINLINE Spec bsdfSampleF(const BSDF &b, V3 woW, V3 *wiW, float u0, float u1, float *pdf, int type, int *sampledType) {
+PG_NI_BSDF Spec bsdfSampleF(const BSDF &b, V3 woW, V3 *wiW, float u0, float u1, float *pdf, int type, int *sampledType) {
     int matchingComps = bsdfNumComponents(b, type);
     if (matchingComps == 0) {
         *pdf = 0;
@@ -402,7 +402,7 @@ PG_HD void makeMaterialLobes(int tag, const float *mp, bool allowMultipleLobes, 
     }
 }
 
-PG_HD_NOINLINE void makeBSDF(const SurfInt &it, const MatLobes *table, int mat, const float *mp, float wvl0, BSDF *b) {
+PG_NI_BSDF void makeBSDF(const SurfInt &it, const MatLobes *table, int mat, const float *mp, float wvl0, BSDF *b) {
     b->ns = it.ns;
     b->ng = it.n;
     b->ss = normalize(it.dpdus);

@@ -52,7 +52,7 @@ PG_HD Spec areaLightL(const DevScene &sc, int li, V3 n, V3 w) {
 }
 
 // Light::Sample_Li.  Returns Li; fills wi, pdf and the point the visibility ray aims at.
-PG_HD_NOINLINE Spec lightSampleLi(const DevScene &sc, int li, const SurfInt &it, float u0, float u1, V3 *wi, float *pdf, ShapeSample *pL) {
+PG_NI_DIRECT Spec lightSampleLi(const DevScene &sc, int li, const SurfInt &it, float u0, float u1, V3 *wi, float *pdf, ShapeSample *pL) {
     int tag = PG_LD(sc.lightTag + li);
     const float *lp = sc.lightParams + PBRTGPU_LIGHT_STRIDE * (size_t)li;
     pL->pError = v3(0, 0, 0);
@@ -107,7 +107,7 @@ PG_HD_NOINLINE Spec lightSampleLi(const DevScene &sc, int li, const SurfInt &it,
     return loadSpec(lp);
 }
 
-PG_HD_NOINLINE float lightPdfLi(const DevScene &sc, int li, const SurfInt &it, V3 wi) {
+PG_NI_DIRECT float lightPdfLi(const DevScene &sc, int li, const SurfInt &it, V3 wi) {
     int tag = PG_LD(sc.lightTag + li);
     if (tag == PBRTGPU_LIGHT_DIFFUSE_AREA || tag == PBRTGPU_LIGHT_PORTAL_AREA)
         return shapePdfRef(sc.bvh, PG_LD(sc.lightPrim + li), it.p, it.pError, it.n, wi);
@@ -170,7 +170,7 @@ PG_HD_NOINLINE void estimateDirectPortal(const DevScene &sc, int li, const SurfI
 // in one piece.  The path integrator's shade stage has the same steps spread over its phases
 // (integrator_stages.h); this form serves Integrator "directlighting", which calls it once per
 // light sample.  `scale` multiplies both contributions (throughput / pick pdf or / nSamples).
-PG_HD_NOINLINE void estimateDirectRays(const DevScene &sc, int li, const SurfInt &it, const BSDF &bsdf, float uL0, float uL1, float uS0,
+PG_NI_DIRECT void estimateDirectRays(const DevScene &sc, int li, const SurfInt &it, const BSDF &bsdf, float uL0, float uL1, float uS0,
                                        float uS1, Spec scale, NeeRequest *out, bool *culled) {
     out->hasShadow = out->hasClosest = false;
     out->light = -1;

@@ -165,7 +165,7 @@ PG_HD void stageRaygen(const WaveParams &w, int slot) {
 }
 
 // Interaction::n and emission of a hit, for SurfaceInteraction::Le(w)
-PG_HD_NOINLINE SurfInt hitInteraction(const DevScene &sc, int prim, float b0, float b1, float b2, const Ray &ray) {
+PG_NI_INTERACTION SurfInt hitInteraction(const DevScene &sc, int prim, float b0, float b1, float b2, const Ray &ray) {
     const F4 *tp = sc.bvh.tris + 3 * (size_t)prim;
     int tag = f2i(PG_LDG(tp).w);
     int type = tag & kTagTypeMask;

@@ -28,7 +28,7 @@ struct SurfInt {
 PG_HD V3 loadV3(const float *p) { return v3(PG_LD(p), PG_LD(p + 1), PG_LD(p + 2)); }
 
 // Triangle hit record.  tri = the slot's three float4 (p0,tag) (p1,-) (p2,-).
-PG_HD_NOINLINE SurfInt triangleInteraction(const F4 *tri, int flags, const float *nrm, const float *uvs, const float *tan, float b0,
+PG_NI_INTERACTION SurfInt triangleInteraction(const F4 *tri, int flags, const float *nrm, const float *uvs, const float *tan, float b0,
                                   float b1, float b2, V3 rayD) {
     F4 a = PG_LDG(tri), b = PG_LDG(tri + 1), c = PG_LDG(tri + 2);
     V3 p0 = v3(a.x, a.y, a.z), p1 = v3(b.x, b.y, b.z), p2 = v3(c.x, c.y, c.z);
@@ -106,7 +106,7 @@ PG_HD SurfInt transformInteraction(const M44 &o2w, const M44 &w2o, V3 pObj, V3 p
 }
 
 // AAPlaneShape hit record: hard-coded dpdu/dpdv/pError (plane.cpp:32-50).
-PG_HD_NOINLINE SurfInt aaplaneInteraction(const Ray &ray, const float *rec, int flags) {
+PG_NI_INTERACTION SurfInt aaplaneInteraction(const Ray &ray, const float *rec, int flags) {
     float t;
     V3 pHit;
     aaplaneTest(ray, rec, &t, &pHit);  // recompute the object-space hit point; ray.tMax must admit the recorded hit
@@ -119,7 +119,7 @@ PG_HD_NOINLINE SurfInt aaplaneInteraction(const Ray &ray, const float *rec, int 
 }
 
 // Sphere hit record (sphere.cpp:107-152).
-PG_HD_NOINLINE SurfInt sphereInteraction(const Ray &ray, const float *rec, int flags) {
+PG_NI_INTERACTION SurfInt sphereInteraction(const Ray &ray, const float *rec, int flags) {
     SphereParams sp = loadSphere(rec);
     float t, phi;
     V3 pHit;

@@ -90,7 +90,7 @@ PG_HD V3 sphericalDirection(float sinT, float cosT, float phi, V3 x, V3 y, V3 z)
 }
 
 // Shape::Sample(ref, u, &pdf): area sample converted to solid angle; Sphere overrides it.
-PG_HD_NOINLINE ShapeSample shapeSampleRef(const DevBVH &bvh, int slot, int flags, const float *triN, V3 refP, V3 refPError, V3 refN,
+PG_NI_DIRECT ShapeSample shapeSampleRef(const DevBVH &bvh, int slot, int flags, const float *triN, V3 refP, V3 refPError, V3 refN,
                                  float u0, float u1, float *pdf) {
     const F4 *tp = bvh.tris + 3 * (size_t)slot;
     int tag = f2i(PG_LDG(tp).w);

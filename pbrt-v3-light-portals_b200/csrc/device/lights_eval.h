@@ -11,7 +11,7 @@ namespace pg {
 enum { kInfRow = 40, kInfMargCdf = 4, kInfMargInt = 5 };
 
 // Shape::Pdf(ref, wi) for one primitive slot (Sphere::Pdf overrides it outside the sphere).
-PG_HD_NOINLINE float shapePdfRef(const DevBVH &bvh, int slot, V3 refP, V3 refPError, V3 refN, V3 wi) {
+PG_NI_DIRECT float shapePdfRef(const DevBVH &bvh, int slot, V3 refP, V3 refPError, V3 refN, V3 wi) {
     const F4 *tp = bvh.tris + 3 * (size_t)slot;
     F4 a = PG_LDG(tp);
     int tag = f2i(a.w);

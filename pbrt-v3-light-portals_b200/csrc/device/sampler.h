@@ -128,7 +128,7 @@ PG_HD float scrambledRadicalInverseBase(unsigned base, unsigned long long magic,
 }
 
 // HaltonSampler::SampleDimension, halton.cpp:118-127
-PG_HD_NOINLINE float haltonSample(const HaltonParams &h, long long index, int dim) {
+PG_NI_SAMPLER float haltonSample(const HaltonParams &h, long long index, int dim) {
     if (h.sampleAtPixelCenter && (dim == 0 || dim == 1)) return 0.5f;
     if (dim == 0) {
         unsigned long long a = (unsigned long long)(index >> h.baseExponents[0]);

@@ -56,7 +56,14 @@ struct BSDF {
     float eta;
     float etaOverride;  // 0, or etaT of all lobes (dispersive_glass)
     int nLobes;
-    const Lobe *lobes;  // into the material table
+    // pointer into the material table, kept as two words so that the record is 4-byte aligned and an odd
+    // number of words long with its neighbours (k_shade_sync keeps one per thread in shared memory)
+    unsigned lobesLo, lobesHi;
+    PG_HD const Lobe *lobePtr() const { return (const Lobe *)(((unsigned long long)lobesHi << 32) | lobesLo); }
+    PG_HD void setLobes(const Lobe *p) {
+        unsigned long long v = (unsigned long long)p;
+        lobesLo = (unsigned)v, lobesHi = (unsigned)(v >> 32);
+    }
 };
 
 // ---- local-frame trigonometry, reflection.h:52-92

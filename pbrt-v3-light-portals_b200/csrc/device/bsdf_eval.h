@@ -164,11 +164,11 @@ PG_HD V3 bsdfLocalToWorld(const BSDF &b, V3 v) {
               b.ss.z * v.x + b.ts.z * v.y + b.ns.z * v.z);
 }
 // etaT of lobe i: the material table's, or the per-path value of a dispersive material
-PG_HD float lobeEtaB(const BSDF &b, int i) { return b.etaOverride != 0.f ? b.etaOverride : b.lobes[i].etaB; }
+PG_HD float lobeEtaB(const BSDF &b, int i) { return b.etaOverride != 0.f ? b.etaOverride : b.lobePtr()[i].etaB; }
 PG_HD int bsdfNumComponents(const BSDF &b, int flags) {
     int n = 0;
     for (int i = 0; i < b.nLobes; ++i)
-        if (lobeMatches(b.lobes[i], flags)) ++n;
+        if (lobeMatches(b.lobePtr()[i], flags)) ++n;
     return n;
 }
 
@@ -178,9 +178,9 @@ PG_NI_BSDF Spec bsdfF(const BSDF &b, V3 woW, V3 wiW, int flags) {
     bool reflect = dot(wiW, b.ng) * dot(woW, b.ng) > 0;
     Spec f = spec(0.f);
     for (int i = 0; i < b.nLobes; ++i)
-        if (lobeMatches(b.lobes[i], flags) && ((reflect && (b.lobes[i].type & BSDF_REFLECTION)) ||
-                                               (!reflect && (b.lobes[i].type & BSDF_TRANSMISSION))))
-            f += lobeF(b.lobes[i], lobeEtaB(b, i), wo, wi);
+        if (lobeMatches(b.lobePtr()[i], flags) && ((reflect && (b.lobePtr()[i].type & BSDF_REFLECTION)) ||
+                                               (!reflect && (b.lobePtr()[i].type & BSDF_TRANSMISSION))))
+            f += lobeF(b.lobePtr()[i], lobeEtaB(b, i), wo, wi);
     return f;
 }
 
@@ -191,9 +191,9 @@ PG_NI_BSDF float bsdfPdf(const BSDF &b, V3 woW, V3 wiW, int flags) {
     float pdf = 0.f;
     int matchingComps = 0;
     for (int i = 0; i < b.nLobes; ++i)
-        if (lobeMatches(b.lobes[i], flags)) {
+        if (lobeMatches(b.lobePtr()[i], flags)) {
             ++matchingComps;
-            pdf += lobePdf(b.lobes[i], lobeEtaB(b, i), wo, wi);
+            pdf += lobePdf(b.lobePtr()[i], lobeEtaB(b, i), wo, wi);
         }
     return matchingComps > 0 ? pdf / matchingComps : 0.f;
 }
@@ -209,11 +209,11 @@ PG_NI_BSDF Spec bsdfSampleF(const BSDF &b, V3 woW, V3 *wiW, float u0, float u1, 
     if (comp > matchingComps - 1) comp = matchingComps - 1;
     int which = -1, count = comp;
     for (int i = 0; i < b.nLobes; ++i)
-        if (lobeMatches(b.lobes[i], type) && count-- == 0) {
+        if (lobeMatches(b.lobePtr()[i], type) && count-- == 0) {
             which = i;
             break;
         }
-    const Lobe &bx = b.lobes[which];
+    const Lobe &bx = b.lobePtr()[which];
     float uR = minf(u0 * matchingComps - comp, kOneMinusEpsilon);
     V3 wi, wo = bsdfWorldToLocal(b, woW);
     // the reference returns here without touching *pdf / *sampledType (reflection.cpp:779);
@@ -233,15 +233,15 @@ PG_NI_BSDF Spec bsdfSampleF(const BSDF &b, V3 woW, V3 *wiW, float u0, float u1, 
     *wiW = bsdfLocalToWorld(b, wi);
     if (!(bx.type & BSDF_SPECULAR) && matchingComps > 1)
         for (int i = 0; i < b.nLobes; ++i)
-            if (i != which && lobeMatches(b.lobes[i], type)) *pdf += lobePdf(b.lobes[i], lobeEtaB(b, i), wo, wi);
+            if (i != which && lobeMatches(b.lobePtr()[i], type)) *pdf += lobePdf(b.lobePtr()[i], lobeEtaB(b, i), wo, wi);
     if (matchingComps > 1) *pdf /= matchingComps;
     if (!(bx.type & BSDF_SPECULAR)) {
         bool reflect = dot(*wiW, b.ng) * dot(woW, b.ng) > 0;
         f = spec(0.f);
         for (int i = 0; i < b.nLobes; ++i)
-            if (lobeMatches(b.lobes[i], type) && ((reflect && (b.lobes[i].type & BSDF_REFLECTION)) ||
-                                                  (!reflect && (b.lobes[i].type & BSDF_TRANSMISSION))))
-                f += lobeF(b.lobes[i], lobeEtaB(b, i), wo, wi);
+            if (lobeMatches(b.lobePtr()[i], type) && ((reflect && (b.lobePtr()[i].type & BSDF_REFLECTION)) ||
+                                                  (!reflect && (b.lobePtr()[i].type & BSDF_TRANSMISSION))))
+                f += lobeF(b.lobePtr()[i], lobeEtaB(b, i), wo, wi);
     }
     return f;
 }
@@ -408,7 +408,7 @@ PG_NI_BSDF void makeBSDF(const SurfInt &it, const MatLobes *table, int mat, cons
     b->ss = normalize(it.dpdus);
     b->ts = cross(b->ns, b->ss);
     const MatLobes *m = table + mat;
-    b->lobes = m->lobes;
+    b->setLobes(m->lobes);
     b->nLobes = PG_LD(&m->nLobes);
     b->eta = PG_LD(&m->eta);
     b->etaOverride = 0.f;

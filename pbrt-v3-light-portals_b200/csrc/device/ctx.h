@@ -41,6 +41,7 @@ struct pbrtgpu_ctx {
     int *dPrimes = nullptr, *dPrimeSums = nullptr;  // first 1000 primes and their running sums
     // wavefront state of the path integrator (render.cu), grown on demand
     pg::DeviceBuffer wave[24];
+    pg::DeviceBuffer waveParams;  // the current batch's WaveParams, read by the shade / raygen / resolve kernels
     pg::DeviceBuffer lightDist;                     // {func[n], cdf[n+1]} x {uniform, power}: the light-pick distributions
     float lightFuncInt[2] = {0, 0};
     pg::DeviceBuffer filterTable;
@@ -62,6 +63,7 @@ struct pbrtgpu_ctx {
     bool tracePersistent = true;
     bool traceFused = true;   // one traversal launch per depth for path + next-event + shadow rays
     bool shadeSync = true;
+    bool shadeSmemSet = false;  // k_shade_sync's shared-memory opt-in done on this device
     int shadeBlock = 1024;
     int fetchThreshold = 12;
     int phaseBias = 16;

@@ -87,8 +87,20 @@ struct NoSync {
     PG_HD void operator()() const {}
 };
 
+// The two records that live across all phases and are handed by reference to the out-of-line leaves.  On the
+// GPU k_shade_sync keeps one per thread in SHARED memory: as locals they sit on the per-thread stack, and
+// 1024 threads x ~1 KB of stack is several times the L1 (ncu r01e: three quarters of the kernel's L2 traffic
+// and most of its DRAM traffic were local-memory sectors).  37 words: odd, so the threads of a warp hit 32
+// different banks when they read the same member.
+struct ShadeScratch {
+    SurfInt it;
+    BSDF bsdf;
+    int pad;
+};
+static_assert(sizeof(ShadeScratch) == 37 * 4, "ShadeScratch must stay an odd number of words");
+
 template <class Sync>
-PG_HD void stageShadePhased(const WaveParams &w, int depth, int cur, int pos, bool active, Sync sync) {
+PG_HD void stageShadePhased(const WaveParams &w, int depth, int cur, int pos, bool active, Sync sync, ShadeScratch &scr) {
     const int flagsNS = BSDF_ALL & ~BSDF_SPECULAR;
     // ---- phase 0: path state, the hit record -> SurfaceInteraction, emitted light (path.cpp:91-96)
     int slot = 0, prim = 0, flags = 0, bounces = 0, mat = -1;
@@ -96,7 +108,7 @@ PG_HD void stageShadePhased(const WaveParams &w, int depth, int cur, int pos, bo
     Ray ray, next;
     Spec L = spec(0.f), beta = spec(0.f);
     float wvl0 = 0, etaScale = 0;
-    SurfInt it;
+    SurfInt &it = scr.it;
     if (active) {
         slot = w.qSlot[cur][pos];
         ray = loadRay(w.rays[cur], pos);
@@ -125,7 +137,7 @@ PG_HD void stageShadePhased(const WaveParams &w, int depth, int cur, int pos, bo
     // ---- phase 1: the material's BSDF (path.cpp:106-107)
     PathSampler smp;
     smp.index = 0, smp.dim = 0;
-    BSDF bsdf;
+    BSDF &bsdf = scr.bsdf;
     bsdf.nLobes = 0;
     if (scatter) {
         smp.index = w.hIndex[slot];
@@ -280,7 +292,10 @@ PG_HD void stageShadePhased(const WaveParams &w, int depth, int cur, int pos, bo
     }
 }
 
-PG_HD void stageShade(const WaveParams &w, int depth, int cur, int pos) { stageShadePhased(w, depth, cur, pos, true, NoSync()); }
+PG_HD void stageShade(const WaveParams &w, int depth, int cur, int pos) {
+    ShadeScratch scr;
+    stageShadePhased(w, depth, cur, pos, true, NoSync(), scr);
+}
 
 // ---- stage 3 for Integrator "directlighting": DirectLightingIntegrator::Li (directlighting.cpp:63-98)
 // at one vertex.  Direct light from all lights (UniformSampleAllLights, integrator.cpp:69-98, with the

@@ -22,7 +22,7 @@ struct SurfInt {
     V3 ns;     // shading.n
     V3 dpdus;  // shading.dpdu
     V3 wo;
-    bool wvlsLost;  // the record went through Transform::operator()(SurfaceInteraction), which drops wvls
+    int wvlsLost;   // the record went through Transform::operator()(SurfaceInteraction), which drops wvls
 };
 
 PG_HD V3 loadV3(const float *p) { return v3(PG_LD(p), PG_LD(p + 1), PG_LD(p + 2)); }

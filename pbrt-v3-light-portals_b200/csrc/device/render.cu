@@ -30,7 +30,21 @@ namespace pg {
 
 constexpr int kStageBlock = 128;
 
-__global__ void __launch_bounds__(kStageBlock) k_raygen(WaveParams w) {
+// The kernels that call out-of-line device functions (Halton digits, hit records, BSDFs, lights) hand them
+// w.sc / w.hal BY REFERENCE.  A by-value __global__ parameter whose address is taken is copied by every
+// thread to its own stack first (ptxas: ~1.4 KB of "stack frame" = sizeof(WaveParams) + the real locals), and
+// the callees then read scene pointers through local memory: 1024 threads x 0.8 KB per SM, far more than
+// the L1 holds.  Those kernels therefore read ONE copy of the parameters from global memory (WaveParams *,
+// written per batch by k_set_wave, stream-ordered); every lane loads the same address, which is one sector.
+__global__ void k_set_wave(WaveParams w, WaveParams *dst) {
+    const int *src = reinterpret_cast<const int *>(&w);
+    int *d = reinterpret_cast<int *>(dst);
+    for (int i = threadIdx.x; i < (int)(sizeof(WaveParams) / sizeof(int)); i += blockDim.x) d[i] = src[i];
+}
+static_assert(sizeof(WaveParams) % sizeof(int) == 0, "WaveParams is copied word by word");
+
+__global__ void __launch_bounds__(kStageBlock) k_raygen(const WaveParams *__restrict__ wp) {
+    const WaveParams &w = *wp;
     int stride = gridDim.x * blockDim.x;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < w.nSlots; i += stride) stageRaygen(w, i);
 }
@@ -159,13 +173,15 @@ __global__ void __launch_bounds__(kTraceBlock, kPersistMinBlocks) k_ptrace_nee(W
 }
 
 // the emitter lookup / MIS weight of the rays k_ptrace_nee traced
-__global__ void __launch_bounds__(kStageBlock) k_nee_resolve(WaveParams w, int depth) {
+__global__ void __launch_bounds__(kStageBlock) k_nee_resolve(const WaveParams *__restrict__ wp, int depth) {
+    const WaveParams &w = *wp;
     int n = w.cnt->nNee[depth];
     int stride = gridDim.x * blockDim.x;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) stageNeeResolve(w, i);
 }
 
-__global__ void __launch_bounds__(kStageBlock) k_shade(WaveParams w, int depth, int cur) {
+__global__ void __launch_bounds__(kStageBlock) k_shade(const WaveParams *__restrict__ wp, int depth, int cur) {
+    const WaveParams &w = *wp;
     int n = w.cnt->nHit[depth];
     int stride = gridDim.x * blockDim.x;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) stageShade(w, depth, cur, w.hitIdx[i]);
@@ -177,18 +193,26 @@ struct BlockSync {
     __device__ __forceinline__ void operator()() const { __syncthreads(); }
 };
 template <int BLOCK, int PER_SM>
-__global__ void __launch_bounds__(BLOCK, PER_SM) k_shade_sync(WaveParams w, int depth, int cur) {
+__global__ void __launch_bounds__(BLOCK, PER_SM) k_shade_sync(const WaveParams *__restrict__ wp, int depth, int cur) {
+    const WaveParams &w = *wp;
     int n = w.cnt->nHit[depth];
     int stride = gridDim.x * blockDim.x;
+#ifdef PG_SHADE_LOCAL_SCRATCH
+    ShadeScratch scr;
+#else
+    extern __shared__ __align__(16) unsigned char pgShadeSmem[];  // BLOCK * sizeof(ShadeScratch), see shadeSmemBytes
+    ShadeScratch &scr = reinterpret_cast<ShadeScratch *>(pgShadeSmem)[threadIdx.x];
+#endif
     for (int base = blockIdx.x * blockDim.x; base < n; base += stride) {
         int i = base + threadIdx.x;
         bool active = i < n;
-        stageShadePhased(w, depth, cur, active ? w.hitIdx[i] : 0, active, BlockSync());
+        stageShadePhased(w, depth, cur, active ? w.hitIdx[i] : 0, active, BlockSync(), scr);
     }
 }
 
 // Integrator "directlighting": one vertex per thread, the block re-synchronised at every vertex
-__global__ void __launch_bounds__(512, 1) k_shade_direct(WaveParams w, int depth, int cur) {
+__global__ void __launch_bounds__(512, 1) k_shade_direct(const WaveParams *__restrict__ wp, int depth, int cur) {
+    const WaveParams &w = *wp;
     int n = w.cnt->nHit[depth];
     int stride = gridDim.x * blockDim.x;
     for (int base = blockIdx.x * blockDim.x; base < n; base += stride) {

@@ -116,6 +116,7 @@ void pbrtgpu_destroy(pbrtgpu_ctx *ctx) {
     if (ctx->dTraversalCounts) cudaFree(ctx->dTraversalCounts);
     for (auto &b : ctx->wave)
         if (b.p) cudaFree(b.p);
+    if (ctx->waveParams.p) cudaFree(ctx->waveParams.p);
     if (ctx->lightDist.p) cudaFree(ctx->lightDist.p);
     if (ctx->filterTable.p) cudaFree(ctx->filterTable.p);
     if (ctx->ownStream && ctx->stream) cudaStreamDestroy(ctx->stream);

@@ -47,7 +47,7 @@ struct MatLobes {  // what ComputeScatteringFunctions adds for one material (bsd
     int nLobes;
     float eta;       // BSDF::eta
     int dispersive;  // eta (and every lobe's etaT) follows the path's wavelength
-    int pad;
+    int shadeClass;  // 0: one Lambertian lobe; 1: anything else -- the hit queue is split by it (render.cu:splitHits)
     Lobe lobes[kMaxLobes];
 };
 

@@ -107,7 +107,9 @@ PG_HD bool primitiveAccepts(const DevBVH &bvh, int slot, const Ray &ray) {
         return triangleTest(ray, v3(a.x, a.y, a.z), v3(b.x, b.y, b.z), v3(c.x, c.y, c.z), &t, &b0, &b1);
     }
     if (type == 1) return aaplaneTest(ray, bvh.planeParams + 48 * (size_t)(tag >> kTagShapeShift), &t, nullptr);
-    return sphereTest(ray, bvh.sphereParams + 48 * (size_t)(tag >> kTagShapeShift), &t, nullptr, nullptr, nullptr);
+    const float *sph = bvh.sphereParams + 48 * (size_t)(tag >> kTagShapeShift);
+    if (sphereDiscriminantNegative(ray, sph)) return false;  // what sphereTest would find out the long way
+    return sphereTest(ray, sph, &t, nullptr, nullptr, nullptr);
 }
 
 // Closest hit (ANY = false): ray.tMax shrinks as in GeometricPrimitive::

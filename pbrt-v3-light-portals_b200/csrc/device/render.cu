@@ -129,9 +129,27 @@ __global__ void __launch_bounds__(kTraceBlock, kPersistMinBlocks) k_ptrace_fused
 }
 
 // hit / miss positions of the depth-d queue, in queue order (so that k_shade reads its inputs nearly in order)
+// Hits on plain Lambertian materials fill hitIdx from the front, hits on everything else (plastic, uber, glass,
+// metal: microfacet or specular lobes, several lobes of which one is picked per sample) from the back: the
+// shade kernel walks the two runs one after the other, so all but one of its warps shade a single class
+// instead of every warp paying for the longest branch of a mixed one.
 __device__ __forceinline__ void splitHits(const WaveParams &w, int depth, bool wantMiss, int i) {
-    if (__float_as_int(w.hits[i].x) >= 0) w.hitIdx[atomicIncInt(&w.cnt->nHit[depth])] = i;
-    else if (wantMiss) w.missIdx[atomicIncInt(&w.cnt->nMiss[depth])] = i;
+    int prim = __float_as_int(w.hits[i].x);
+    if (prim >= 0) {
+        bool multi = false;
+        if (w.sortHits && w.sc.primMaterial) {
+            int m = __ldg(w.sc.primMaterial + prim);
+            if (m >= 0) multi = __ldg(&w.sc.matLobes[m].shadeClass) != 0;
+        }
+        if (multi) w.hitIdx[w.nSlots - 1 - atomicIncInt(&w.cnt->nHitB[depth])] = i;
+        else w.hitIdx[atomicIncInt(&w.cnt->nHit[depth])] = i;
+    } else if (wantMiss)
+        w.missIdx[atomicIncInt(&w.cnt->nMiss[depth])] = i;
+}
+__device__ __forceinline__ int hitQueueLen(const WaveParams &w, int depth) { return w.cnt->nHit[depth] + w.cnt->nHitB[depth]; }
+__device__ __forceinline__ int hitQueueAt(const WaveParams &w, int depth, int i) {
+    int nA = w.cnt->nHit[depth];
+    return i < nA ? w.hitIdx[i] : w.hitIdx[w.nSlots - 1 - (i - nA)];
 }
 __global__ void __launch_bounds__(kStageBlock) k_split_hits(WaveParams w, int depth, bool wantMiss) {
     int n = w.cnt->nActive[depth];
@@ -182,9 +200,9 @@ __global__ void __launch_bounds__(kStageBlock) k_nee_resolve(const WaveParams *_
 
 __global__ void __launch_bounds__(kStageBlock) k_shade(const WaveParams *__restrict__ wp, int depth, int cur) {
     const WaveParams &w = *wp;
-    int n = w.cnt->nHit[depth];
+    int n = hitQueueLen(w, depth);
     int stride = gridDim.x * blockDim.x;
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) stageShade(w, depth, cur, w.hitIdx[i]);
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) stageShade(w, depth, cur, hitQueueAt(w, depth, i));
 }
 
 // One 384-thread block per SM, all of whose warps walk the phases of stageShadePhased together
@@ -195,7 +213,7 @@ struct BlockSync {
 template <int BLOCK, int PER_SM>
 __global__ void __launch_bounds__(BLOCK, PER_SM) k_shade_sync(const WaveParams *__restrict__ wp, int depth, int cur) {
     const WaveParams &w = *wp;
-    int n = w.cnt->nHit[depth];
+    int n = hitQueueLen(w, depth);
     int stride = gridDim.x * blockDim.x;
 #ifdef PG_SHADE_LOCAL_SCRATCH
     ShadeScratch scr;
@@ -206,19 +224,19 @@ __global__ void __launch_bounds__(BLOCK, PER_SM) k_shade_sync(const WaveParams *
     for (int base = blockIdx.x * blockDim.x; base < n; base += stride) {
         int i = base + threadIdx.x;
         bool active = i < n;
-        stageShadePhased(w, depth, cur, active ? w.hitIdx[i] : 0, active, BlockSync(), scr);
+        stageShadePhased(w, depth, cur, active ? hitQueueAt(w, depth, i) : 0, active, BlockSync(), scr);
     }
 }
 
 // Integrator "directlighting": one vertex per thread, the block re-synchronised at every vertex
 __global__ void __launch_bounds__(512, 1) k_shade_direct(const WaveParams *__restrict__ wp, int depth, int cur) {
     const WaveParams &w = *wp;
-    int n = w.cnt->nHit[depth];
+    int n = hitQueueLen(w, depth);
     int stride = gridDim.x * blockDim.x;
     for (int base = blockIdx.x * blockDim.x; base < n; base += stride) {
         int i = base + threadIdx.x;
         __syncthreads();
-        if (i < n) stageShadeDirect(w, depth, cur, w.hitIdx[i]);
+        if (i < n) stageShadeDirect(w, depth, cur, hitQueueAt(w, depth, i));
     }
 }
 
@@ -278,11 +296,12 @@ __global__ void k_batch_stats(WaveCounters *cnt, unsigned long long *totals, int
     totals[2] += shadow;
     totals[3] += cnt->scrubbed;
     const int a = cnt->nActive[depths], h = depths < kMaxDepthSlots ? cnt->nHit[depths] : 0, m = depths < kMaxDepthSlots ? cnt->nMiss[depths] : 0;
+    const int hb = depths < kMaxDepthSlots ? cnt->nHitB[depths] : 0;
     for (int d = 0; d <= kMaxDepthSlots; ++d) cnt->nActive[d] = 0;
     for (int d = 0; d < kMaxDepthSlots; ++d)
-        cnt->nShadow[d] = cnt->nNee[d] = cnt->nHit[d] = cnt->nMiss[d] = cnt->fetch[0][d] = cnt->fetch[1][d] = cnt->fetch[2][d] = cnt->nNeeCulled[d] = 0;
+        cnt->nShadow[d] = cnt->nNee[d] = cnt->nHit[d] = cnt->nHitB[d] = cnt->nMiss[d] = cnt->fetch[0][d] = cnt->fetch[1][d] = cnt->fetch[2][d] = cnt->nNeeCulled[d] = 0;
     cnt->scrubbed = 0;
-    if (carry) cnt->nActive[0] = a, cnt->nHit[0] = h, cnt->nMiss[0] = m;
+    if (carry) cnt->nActive[0] = a, cnt->nHit[0] = h, cnt->nHitB[0] = hb, cnt->nMiss[0] = m;
 }
 
 // Film::MergeFilmTile's RGB -> XYZ (film.cpp:125-127), once per pixel at the end

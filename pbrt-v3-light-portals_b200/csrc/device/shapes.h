@@ -273,5 +273,22 @@ PG_HD_NOINLINE bool sphereTest(const Ray &r, const float *rec, float *tOut, V3 *
     return true;
 }
 
+// sphereTest's first exit without the interval arithmetic.  efQuadratic rejects on `discrim < 0`, and discrim is
+// computed in double from the VALUE parts of A, B and C alone (efloat.h:257-259); those are plain float
+// expressions of the transformed ray, evaluated here in the same order.  True means sphereTest(r, rec, ...)
+// returns false -- exactly, not approximately.  Used where most rays miss the sphere by far (the MIS-ray
+// cull of integrator_stages.h): the full test is ~10x the instructions.
+PG_HD bool sphereDiscriminantNegative(const Ray &r, const float *rec) {
+    float radius = rec[0];
+    M44 w2o = loadM44(rec + 32);
+    V3 oErr, dErr;
+    Ray ray = xformRayErr(w2o, r, &oErr, &dErr);
+    float a = ray.d.x * ray.d.x + ray.d.y * ray.d.y + ray.d.z * ray.d.z;
+    float b = 2.f * (ray.d.x * ray.o.x + ray.d.y * ray.o.y + ray.d.z * ray.o.z);
+    float c = ray.o.x * ray.o.x + ray.o.y * ray.o.y + ray.o.z * ray.o.z - radius * radius;
+    double discrim = (double)b * (double)b - 4. * (double)a * (double)c;
+    return discrim < 0.;
+}
+
 }  // namespace pg
 #endif

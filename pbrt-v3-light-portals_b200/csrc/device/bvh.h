@@ -107,9 +107,7 @@ PG_HD bool primitiveAccepts(const DevBVH &bvh, int slot, const Ray &ray) {
         return triangleTest(ray, v3(a.x, a.y, a.z), v3(b.x, b.y, b.z), v3(c.x, c.y, c.z), &t, &b0, &b1);
     }
     if (type == 1) return aaplaneTest(ray, bvh.planeParams + 48 * (size_t)(tag >> kTagShapeShift), &t, nullptr);
-    const float *sph = bvh.sphereParams + 48 * (size_t)(tag >> kTagShapeShift);
-    if (sphereDiscriminantNegative(ray, sph)) return false;  // what sphereTest would find out the long way
-    return sphereTest(ray, sph, &t, nullptr, nullptr, nullptr);
+    return sphereTestGuarded(ray, bvh.sphereParams + 48 * (size_t)(tag >> kTagShapeShift), &t);
 }
 
 // Closest hit (ANY = false): ray.tMax shrinks as in GeometricPrimitive::
@@ -165,7 +163,7 @@ PG_HD bool traverse(const DevBVH &bvh, Ray &ray, Hit *hit, TraverseCounters *cnt
                 } else if (type == 1) {
                     h = aaplaneTest(ray, bvh.planeParams + 48 * (size_t)(tag >> kTagShapeShift), &t, nullptr);
                 } else {
-                    h = sphereTest(ray, bvh.sphereParams + 48 * (size_t)(tag >> kTagShapeShift), &t, nullptr, nullptr, nullptr);
+                    h = sphereTestGuarded(ray, bvh.sphereParams + 48 * (size_t)(tag >> kTagShapeShift), &t);
                 }
                 if (h) {
                     if (ANY) return true;

@@ -273,12 +273,18 @@ PG_HD_NOINLINE bool sphereTest(const Ray &r, const float *rec, float *tOut, V3 *
     return true;
 }
 
-// sphereTest's first exit without the interval arithmetic.  efQuadratic rejects on `discrim < 0`, and discrim is
-// computed in double from the VALUE parts of A, B and C alone (efloat.h:257-259); those are plain float
-// expressions of the transformed ray, evaluated here in the same order.  True means sphereTest(r, rec, ...)
-// returns false -- exactly, not approximately.  Used where most rays miss the sphere by far (the MIS-ray
-// cull of integrator_stages.h): the full test is ~10x the instructions.
-PG_HD bool sphereDiscriminantNegative(const Ray &r, const float *rec) {
+// Cheap, EXACT rejections in front of sphereTest.  EFloat carries a value v and an interval [low, high] with
+// low <= v <= high (every efloat.h operation rounds the interval outwards and computes v from the operands'
+// v alone), and sphereTest's early exits are
+//     efQuadratic: discrim < 0                (double, from A.v, B.v, C.v only; efloat.h:257-259)
+//     t0.high > ray.tMax  ||  t1.low <= 0     (sphere.cpp:70)
+// The value parts are plain float expressions of the transformed ray, evaluated here in the same order, so
+// "discrim < 0", "t0.v > tMax" (=> t0.high > tMax) and "t1.v <= 0" (=> t1.low <= 0) each imply that
+// sphereTest returns false.  A NaN on either side makes a comparison false and sends the ray to the full test.
+// Why it matters: a shadow ray aimed at a sampled point of a sphere light ends just short of it
+// (tMax = 1 - ShadowEpsilon, t0 ~ 1), so EVERY such ray used to run the ~1100-instruction interval version
+// only to be turned away by `t0.high > tMax` (ncu r01g: a quarter of k_ptrace_fused's instructions).
+PG_HD bool sphereRejects(const Ray &r, const float *rec) {
     float radius = rec[0];
     M44 w2o = loadM44(rec + 32);
     V3 oErr, dErr;
@@ -287,7 +293,20 @@ PG_HD bool sphereDiscriminantNegative(const Ray &r, const float *rec) {
     float b = 2.f * (ray.d.x * ray.o.x + ray.d.y * ray.o.y + ray.d.z * ray.o.z);
     float c = ray.o.x * ray.o.x + ray.o.y * ray.o.y + ray.o.z * ray.o.z - radius * radius;
     double discrim = (double)b * (double)b - 4. * (double)a * (double)c;
-    return discrim < 0.;
+    if (discrim < 0.) return true;
+    float root = (float)sqrt(discrim);
+    float q = (b < 0) ? -.5f * (b - root) : -.5f * (b + root);
+    float t0 = q / a, t1 = c / q;
+    if (t0 > t1) {
+        float tmp = t0;
+        t0 = t1;
+        t1 = tmp;
+    }
+    return t0 > ray.tMax || t1 <= 0;
+}
+PG_HD bool sphereTestGuarded(const Ray &r, const float *rec, float *tOut) {
+    if (sphereRejects(r, rec)) return false;
+    return sphereTest(r, rec, tOut, nullptr, nullptr, nullptr);
 }
 
 }  // namespace pg

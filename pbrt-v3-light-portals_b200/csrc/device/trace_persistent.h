@@ -183,7 +183,7 @@ __device__ __forceinline__ void tracePersistent(const DevBVH &bvh, Source source
             } else if (type == 1) {
                 h = aaplaneTest(ray, bvh.planeParams + 48 * (size_t)(tag >> kTagShapeShift), &t, nullptr);
             } else {
-                h = sphereTest(ray, bvh.sphereParams + 48 * (size_t)(tag >> kTagShapeShift), &t, nullptr, nullptr, nullptr);
+                h = sphereTestGuarded(ray, bvh.sphereParams + 48 * (size_t)(tag >> kTagShapeShift), &t);
             }
             if (h) {
                 if (any) occluded = true;

@@ -30,10 +30,17 @@ inline std::vector<int> firstPrimes(int n = kPrimeTableSize) {
     return primes;
 }
 
-// floor(2^64 / p) + 1 for each prime (see sampler.h: exact a / p for a < 2^32)
+// Division magics, two tables of primes.size() entries back to back (see sampler.h):
+//   [i]      floor(2^64 / p) + 1                     exact a / p = mulhi64(a, .) for a < 2^32
+//   [n + i]  ceil(2^(32 + s) / p), s = floor(log2 p)  exact a / p = mulhi32(a, .) >> s for a < 2^31 (fits 32 bits)
 inline std::vector<unsigned long long> primeMagics(const std::vector<int> &primes) {
     std::vector<unsigned long long> m;
     for (int p : primes) m.push_back(~0ull / (unsigned long long)p + 1);
+    for (int p : primes) {
+        int s = 0;
+        while ((2u << s) <= (unsigned)p) ++s;
+        m.push_back(((1ull << (32 + s)) + (unsigned long long)p - 1) / (unsigned long long)p);
+    }
     return m;
 }
 

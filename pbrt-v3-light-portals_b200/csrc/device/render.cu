@@ -41,6 +41,7 @@ __global__ void k_set_wave(WaveParams w, WaveParams *dst) {
     int *d = reinterpret_cast<int *>(dst);
     for (int i = threadIdx.x; i < (int)(sizeof(WaveParams) / sizeof(int)); i += blockDim.x) d[i] = src[i];
 }
+static_assert(kHaltonPrimes == kPrimeTableSize, "sampler.h and halton_tables.h disagree on the prime table size");
 static_assert(sizeof(WaveParams) % sizeof(int) == 0, "WaveParams is copied word by word");
 
 __global__ void __launch_bounds__(kStageBlock) k_raygen(const WaveParams *__restrict__ wp) {

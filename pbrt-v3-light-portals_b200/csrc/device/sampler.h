@@ -18,6 +18,7 @@ namespace pg {
 
 constexpr int kHaltonMaxResolution = 128;  // halton.cpp:42
 
+constexpr int kHaltonPrimes = 1000;  // entries of the prime tables (= kPrimeTableSize, common/halton_tables.h)
 constexpr int kArrayStartDim = 5;  // GlobalSampler::arrayStartDim (sampler.h:122) -- although this fork's camera sample uses 6 dimensions
 
 struct HaltonParams {
@@ -28,7 +29,7 @@ struct HaltonParams {
     int arrayEndDim;               // GlobalSampler: dimensions [kArrayStartDim, arrayEndDim) hold the sample arrays (sampler.cpp:126-148)
     const int *primes;             // 1000 entries
     const int *primeSums;          // 1000 entries
-    const unsigned long long *primeMagic;  // 1000 entries: floor(2^64 / p) + 1, so that a / p = mulhi64(a, magic) for a < 2^32
+    const unsigned long long *primeMagic;  // 2 x 1000 entries (halton_tables.h:primeMagics): 64-bit magics, then 32-bit ones
     const unsigned short *perms;   // 3,682,913 entries
 };
 
@@ -105,10 +106,51 @@ PG_HD unsigned long long mulhi64(unsigned long long a, unsigned long long b) {
 // magic = floor(2^64 / base) + 1 the product overshoots a / base by less than
 // 2^-32, which cannot carry past the fraction's distance (>= 1 / base) to the
 // next integer -- so the digits are the reference's.
-PG_HD float scrambledRadicalInverseBase(unsigned base, unsigned long long magic, const unsigned short *perm, unsigned long long a) {
+//
+// Indices below 2^31 (every BASELINE configuration: stride 31104 x 4096 spp = 1.3e8) take a shorter loop:
+// with s = floor(log2 base) and m = ceil(2^(32+s) / base) < 2^32, e = m * base - 2^(32+s) lies in (0, base),
+// so a * m / 2^(32+s) = a / base + a * e / (base * 2^(32+s)), and the excess is below 1 / base whenever
+// a * e < 2^(32+s) -- true for a < 2^31 because e < base < 2^(s+1).  Hence mulhi32(a, m) >> s = a / base.
+// All digits but the most significant one are accumulated in 32 bits (before the last step the reversed
+// digits are below base^(k-1) <= a < 2^31); the last step widens to the reference's 64-bit value.
+PG_HD unsigned mulhi32(unsigned a, unsigned b) {
+#if defined(__CUDA_ARCH__)
+    return __umulhi(a, b);
+#else
+    return (unsigned)(((unsigned long long)a * (unsigned long long)b) >> 32);
+#endif
+}
+PG_HD int floorLog2u(unsigned v) {
+#if defined(__CUDA_ARCH__)
+    return 31 - __clz((int)v);
+#else
+    return 31 - __builtin_clz(v);
+#endif
+}
+PG_HD float scrambledRadicalInverseBase(unsigned base, unsigned long long magic, unsigned magic32, const unsigned short *perm,
+                                        unsigned long long a) {
     const float invBase = (float)1 / (float)base;
     unsigned long long reversedDigits = 0;
     float invBaseN = 1;
+    if (a <= 0x7fffffffull) {
+        unsigned a32 = (unsigned)a, rev = 0;
+        if (a32) {
+            const int s = floorLog2u(base);
+            for (;;) {
+                unsigned next = mulhi32(a32, magic32) >> s;
+                unsigned digit = a32 - next * base;
+                unsigned pd = PG_LD(perm + digit);
+                invBaseN *= invBase;
+                if (next == 0) {
+                    reversedDigits = (unsigned long long)rev * base + pd;
+                    break;
+                }
+                rev = rev * base + pd;
+                a32 = next;
+            }
+        }
+        return minf(invBaseN * ((float)reversedDigits + invBase * (float)PG_LD(perm) / (1 - invBase)), kOneMinusEpsilon);
+    }
     while (a > 0xffffffffull) {
         unsigned long long next = a / base;
         unsigned long long digit = a - next * base;
@@ -136,7 +178,8 @@ PG_NI_SAMPLER float haltonSample(const HaltonParams &h, long long index, int dim
     }
     if (dim == 1) return radicalInverseBase(3u, (unsigned long long)(index / h.baseScales[1]));
     unsigned base = (unsigned)PG_LD(h.primes + dim);
-    return scrambledRadicalInverseBase(base, PG_LD(h.primeMagic + dim), h.perms + PG_LD(h.primeSums + dim), (unsigned long long)index);
+    return scrambledRadicalInverseBase(base, PG_LD(h.primeMagic + dim), (unsigned)PG_LD(h.primeMagic + kHaltonPrimes + dim),
+                                       h.perms + PG_LD(h.primeSums + dim), (unsigned long long)index);
 }
 
 // HaltonSampler's constructor (halton.cpp:65-93): scales/exponents that cover

@@ -231,6 +231,18 @@ extern "C" int hostsim_render(void *p, const pbrtgpu_render_params *rp, float *f
     return 0;
 }
 
+// the digit permutation of one dimension (for tests that restate ScrambledRadicalInverse independently)
+extern "C" int hostsim_halton_perm(int dim, int32_t *base, uint16_t *out) {
+    static std::vector<int> primes = firstPrimes();
+    static std::vector<uint16_t> perms = radicalInversePermutations(primes);
+    if (dim < 0 || dim >= (int)primes.size()) return 1;
+    size_t off = 0;
+    for (int i = 0; i < dim; ++i) off += primes[i];
+    *base = primes[dim];
+    for (int i = 0; i < primes[dim]; ++i) out[i] = perms[off + i];
+    return 0;
+}
+
 extern "C" int hostsim_halton(const pbrtgpu_render_params *rp, const int32_t *xy, const int64_t *num, const int32_t *dim, int64_t n, float *out) {
     static std::vector<int> primes = firstPrimes(), sums;
     static std::vector<uint16_t> perms;

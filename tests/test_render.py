@@ -167,6 +167,43 @@ def test_halton_first_dimensions_known_answers(pkg, hostsim_lib):
         assert np.allclose(out, want, rtol=0, atol=1e-7), (dim, out, want)
 
 
+def test_halton_scrambled_digits_against_bigint_restatement(pkg, hostsim_lib):
+    """ScrambledRadicalInverse (lowdiscrepancy.cpp:406-423) restated with Python integers and float32 steps,
+    against the device code's two digit loops: the 32-bit magic-multiply loop (index < 2^31) and the 64-bit
+    one, including indices either side of 2^31 and 2^32 and multiples of the base +- 1."""
+    import ctypes as C
+    hs = load_case(pkg, "tri_soup")
+    p = hs.params.copy()
+    p.sample_bounds[0], p.sample_bounds[1], p.sample_bounds[2], p.sample_bounds[3] = 0, 0, 1, 1  # stride 1: index = sample number
+    rng = np.random.default_rng(11)
+    f32 = np.float32
+    for dim in (2, 3, 7, 31, 100, 500, 999):
+        base = C.c_int32(0)
+        perm = np.zeros(8192, np.uint16)
+        assert hostsim_lib.hostsim_halton_perm(dim, C.byref(base), perm.ctypes.data_as(C.c_void_p)) == 0
+        b = base.value
+        idx = [0, 1, b - 1, b, b + 1, b * b - 1, b * b, 2**31 - 1, 2**31, 2**31 + 1, 2**32 - 1, 2**32, 2**32 + 1, 2**40 + 12345]
+        idx += [int(k) * b + d for k in rng.integers(1, 2**31 // b, 40) for d in (-1, 0, 1)]
+        idx += [int(v) for v in rng.integers(0, 2**31, 200)] + [int(v) for v in rng.integers(2**31, 2**34, 50)]
+        num = np.array(idx, np.int64)
+        n = len(idx)
+        xy = np.zeros((n, 2), np.int32)
+        d = np.full(n, dim, np.int32)
+        out = np.zeros(n, np.float32)
+        hostsim_lib.hostsim_halton(C.byref(p), xy.ctypes.data_as(C.c_void_p), num.ctypes.data_as(C.c_void_p),
+                                   d.ctypes.data_as(C.c_void_p), C.c_int64(n), out.ctypes.data_as(C.c_void_p))
+        inv_base = f32(1) / f32(b)
+        for a, got in zip(idx, out):
+            rev, inv_n = 0, f32(1)
+            while a:
+                a, digit = divmod(a, b)
+                rev = rev * b + int(perm[digit])
+                inv_n = f32(inv_n * inv_base)
+            tail = f32(f32(inv_base * f32(perm[0])) / f32(f32(1) - inv_base))
+            want = min(f32(inv_n * f32(f32(rev) + tail)), f32(np.nextafter(f32(1), f32(0))))
+            assert got == want, (dim, b, got, want)
+
+
 # ---------------------------------------------------------------- GPU
 
 @pytest.mark.gpu

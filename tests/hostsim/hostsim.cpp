@@ -243,6 +243,21 @@ extern "C" int hostsim_halton_perm(int dim, int32_t *base, uint16_t *out) {
     return 0;
 }
 
+// sphereRejects (the cheap exact early-out) next to sphereTest (the interval version) on the same rays:
+// rays = 8 floats each (o.xyz, tMax, d.xyz, -), rec = one PBRTGPU_SPHERE_STRIDE record
+extern "C" int hostsim_sphere_guard(const float *rec, const float *rays, int64_t n, uint8_t *rejects, uint8_t *accepts) {
+    for (int64_t i = 0; i < n; ++i) {
+        Ray r;
+        r.o = v3(rays[8 * i], rays[8 * i + 1], rays[8 * i + 2]);
+        r.tMax = rays[8 * i + 3];
+        r.d = v3(rays[8 * i + 4], rays[8 * i + 5], rays[8 * i + 6]);
+        float t;
+        rejects[i] = sphereRejects(r, rec) ? 1 : 0;
+        accepts[i] = sphereTest(r, rec, &t, nullptr, nullptr, nullptr) ? 1 : 0;
+    }
+    return 0;
+}
+
 extern "C" int hostsim_halton(const pbrtgpu_render_params *rp, const int32_t *xy, const int64_t *num, const int32_t *dim, int64_t n, float *out) {
     static std::vector<int> primes = firstPrimes(), sums;
     static std::vector<uint16_t> perms;

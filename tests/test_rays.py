@@ -185,3 +185,38 @@ def test_gpu_edge_inputs(soup, gpu):
     ids, t, _ = gpu.intersect_closest(bad)
     assert (ids == -1).all()
     assert (gpu.intersect_any(bad) == 0).all()
+
+
+def test_sphere_early_out_never_rejects_a_hit(pkg, hostsim_lib):
+    """shapes.h:sphereRejects claims to be EXACT: whenever it says "rejected", the interval-arithmetic
+    Sphere::Intersect restatement (sphereTest) returns false as well.  Checked on rays of every kind around the
+    spheres of tests/scenes/sphere_lights.pbrt: aimed at the sphere, grazing it, starting inside it, ending
+    just short of it (the shadow-ray case the early-out exists for), and missing it by far."""
+    import ctypes as C
+    hs = pkg.HostScene(os.path.join(os.path.dirname(__file__), "scenes", "sphere_lights.pbrt"))
+    v = hs.view
+    assert v.n_spheres > 0
+    recs = np.ctypeslib.as_array(v.sphere_params, shape=(v.n_spheres, 48)).copy()
+    rng = np.random.default_rng(3)
+    total_rej = total = 0
+    for rec in recs:
+        radius = rec[0]
+        o2w = rec[16:32].reshape(4, 4)
+        centre = o2w[:3, 3].astype(np.float64)
+        n = 40000
+        rays = np.zeros((n, 8), np.float32)
+        org = centre + rng.normal(size=(n, 3)) * radius * rng.choice([0.5, 1.5, 4.0, 50.0], size=(n, 1))
+        on = rng.normal(size=(n, 3))
+        on /= np.linalg.norm(on, axis=1, keepdims=True)
+        target = centre + on * radius * rng.choice([0.0, 0.9, 1.0, 1.0001, 1.1, 3.0], size=(n, 1))
+        rays[:, 0:3] = org
+        rays[:, 4:7] = target - org
+        rays[:, 3] = rng.choice([np.inf, 1.0 - 1e-4, 1.0, 0.5, 2.0], size=n)
+        rej = np.zeros(n, np.uint8)
+        acc = np.zeros(n, np.uint8)
+        hostsim_lib.hostsim_sphere_guard(rec.ctypes.data_as(C.c_void_p), rays.ctypes.data_as(C.c_void_p), C.c_int64(n),
+                                         rej.ctypes.data_as(C.c_void_p), acc.ctypes.data_as(C.c_void_p))
+        assert not np.any((rej == 1) & (acc == 1)), "sphereRejects turned away a ray that Sphere::Intersect accepts"
+        total_rej += int(rej.sum())
+        total += int((acc == 0).sum())
+    assert total_rej > 0.5 * total  # and it is worth having: it catches most of the rays the full test rejects

@@ -72,7 +72,9 @@ enum {
 #define PBRTGPU_LIGHT_STRIDE 48 /* floats per light in light_params: [0..7] scalars, [8..23] LightToWorld, [24..39] WorldToLight */
 
 /* PortalStrategy, lights/portal_arealight.h:12 (same numbering) */
-enum { PBRTGPU_PORTAL_UNIFORM_PORTAL = 0, PBRTGPU_PORTAL_UNIFORM_LIGHT = 1, PBRTGPU_PORTAL_PROJECTION = 2 };
+enum { PBRTGPU_PORTAL_UNIFORM_PORTAL = 0, PBRTGPU_PORTAL_UNIFORM_LIGHT = 1, PBRTGPU_PORTAL_PROJECTION = 2,
+       /* not in the reference: solid-angle sampling of the portal rectangle, alone / one-sample MIS with the BSDF (device/portal.h) */
+       PBRTGPU_PORTAL_SOLIDANGLE = 3, PBRTGPU_PORTAL_SOLIDANGLE_MIS = 4 };
 
 #define PBRTGPU_PLANE_STRIDE 48  /* floats per AAPlaneShape: lo[3] hi[3] ax facingFw area pad[7] O2W[16] W2O[16]   shapes/plane.h:12-40 */
 #define PBRTGPU_SPHERE_STRIDE 48 /* floats per Sphere: radius zMin zMax thetaMin thetaMax phiMax pad[10] O2W[16] W2O[16]  shapes/sphere.h */

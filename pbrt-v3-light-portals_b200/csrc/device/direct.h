@@ -122,8 +122,51 @@ PG_HD float powerHeuristic(float fPdf, float gPdf) {  // PowerHeuristic(1, f, 1,
 
 // The portal branch of EstimateDirect.  u1 is what the reference passes as u1:
 // the SCATTERING sample (Q5); u2 is unused there as well.
+// The two strategies that are NOT the reference's ("solidangle", "solidangle_mis"; portal.h).  One next-event
+// ray per vertex, counted only if its closest hit is this light (NEE_MIS_LIGHT).  p_A = 1 / (sum of the solid
+// angles of the portals in front) for a direction through one of them, else 0.
+//   solidangle      the direction is drawn through a portal:  f |cos| Le / p_A
+//   solidangle_mis  one-sample MIS (Veach 9.2.4) of that technique and BSDF sampling, each taken with
+//                   probability 1/2, balance heuristic:       f |cos| Le / (p_A / 2 + p_B / 2)
+// u1 = the scattering sample, u2 = the light sample of UniformSampleOneLight / AllLights.
+PG_HD_NOINLINE bool estimateDirectPortalSolidAngle(const DevScene &sc, int li, int strat, const float *lightRec, const float *portals, int nPortals,
+                                                   const SurfInt &it, const BSDF &bsdf, float u1x, float u1y, float u2x, float u2y, Spec scale,
+                                                   NeeRequest *out) {
+    const int flagsNS = BSDF_ALL & ~BSDF_SPECULAR;
+    M44 o2w = loadM44(lightRec + 16), w2o = loadM44(lightRec + 32);
+    int sel;
+    SphRect rect;
+    float sumOmega = portalSolidAngles(portals, nPortals, o2w, w2o, it.p, u2x, &sel, &rect);
+    if (!(sumOmega > 0) || sel < 0) return false;  // behind every portal: the caller falls back to sampling the light
+    const float pA = 1 / sumOmega;
+    const bool mis = strat == PBRTGPU_PORTAL_SOLIDANGLE_MIS;
+    V3 wi;
+    Spec f;
+    float pdf;
+    if (!mis || u2y < 0.5f) {
+        wi = normalize(sphRectSample(rect, u1x, u1y) - it.p);
+        f = bsdfF(bsdf, it.wo, wi, flagsNS) * absDot(wi, it.ns);
+        pdf = mis ? 0.5f * pA + 0.5f * bsdfPdf(bsdf, it.wo, wi, flagsNS) : pA;
+    } else {
+        int sampledType;
+        float pB = 0;
+        wi = v3(0, 0, 0);
+        f = bsdfSampleF(bsdf, it.wo, &wi, u1x, u1y, &pB, flagsNS, &sampledType);
+        if (isBlack(f) || !(pB > 0)) return true;
+        f *= absDot(wi, it.ns);
+        pdf = 0.5f * pB + (portalsContainDirection(portals, nPortals, o2w, w2o, it.p, wi) ? 0.5f * pA : 0.f);
+    }
+    if (isBlack(f) || !(pdf > 0)) return true;
+    out->hasClosest = true;
+    out->closestRay = spawnRay(it.p, it.pError, it.n, wi);
+    out->closestContrib = scale * (f / pdf);
+    out->light = li;
+    out->mode = NEE_MIS_LIGHT;
+    return true;
+}
+
 PG_HD_NOINLINE void estimateDirectPortal(const DevScene &sc, int li, const SurfInt &it, const BSDF &bsdf, float u1x, float u1y,
-                                Spec scale, NeeRequest *out) {
+                                float u2x, float u2y, Spec scale, NeeRequest *out) {
     const int flagsNS = BSDF_ALL & ~BSDF_SPECULAR;
     int strat = PG_LD(sc.lightStrategy + li);
     int slot = PG_LD(sc.lightPrim + li);
@@ -134,6 +177,10 @@ PG_HD_NOINLINE void estimateDirectPortal(const DevScene &sc, int li, const SurfI
     int pBegin = PG_LD(sc.lightPortalBegin + li), nPortals = PG_LD(sc.lightPortalBegin + li + 1) - pBegin;
     const float *portals = sc.portalParams + PBRTGPU_PORTAL_STRIDE * (size_t)pBegin;
     M44 w2o = loadM44(lightRec + 32);
+    if (strat == PBRTGPU_PORTAL_SOLIDANGLE || strat == PBRTGPU_PORTAL_SOLIDANGLE_MIS) {
+        if (nPortals > 0 && estimateDirectPortalSolidAngle(sc, li, strat, lightRec, portals, nPortals, it, bsdf, u1x, u1y, u2x, u2y, scale, out)) return;
+        strat = PBRTGPU_PORTAL_UNIFORM_LIGHT;  // behind every portal
+    }
     if (strat != PBRTGPU_PORTAL_UNIFORM_LIGHT) {
         // with no portal at all the loop leaves behindAll = true -> light sampling
         sel = nPortals > 0 ? portalSelect(portals, nPortals, w2o, it.p, u1x, &portalPdf) : -2;
@@ -178,7 +225,7 @@ PG_NI_DIRECT void estimateDirectRays(const DevScene &sc, int li, const SurfInt &
     *culled = false;
     int tag = PG_LD(sc.lightTag + li);
     if (tag == PBRTGPU_LIGHT_PORTAL_AREA) {
-        estimateDirectPortal(sc, li, it, bsdf, uS0, uS1, spec(1.f), out);
+        estimateDirectPortal(sc, li, it, bsdf, uS0, uS1, uL0, uL1, spec(1.f), out);
         if (out->hasClosest) out->closestContrib = scale * out->closestContrib;
         return;
     }

@@ -176,7 +176,7 @@ PG_HD void stageShadePhased(const WaveParams &w, int depth, int cur, int pos, bo
         r.hasShadow = r.hasClosest = false;
         r.light = -1;
         r.mode = NEE_MIS_LIGHT;
-        estimateDirectPortal(w.sc, li, it, bsdf, uS0, uS1, spec(1.f), &r);
+        estimateDirectPortal(w.sc, li, it, bsdf, uS0, uS1, uL0, uL1, spec(1.f), &r);
         if (r.hasClosest) {
             Spec c = beta * (r.closestContrib / pickPdf);
             int np = atomicIncInt(&w.cnt->nNee[depth]);

@@ -104,5 +104,120 @@ PG_HD_NOINLINE void portalSampleProj(const PortalRec &po, const PlaneParams &lig
     *pdf = distanceSquared(refP, sampled) / (absDot(aaplaneNormal(po.pl), -*wi) * (isectLen0 * isectLen1));
 }
 
+// ---- Corrected portal sampling (NOT in the reference; strategies "solidangle" and "solidangle_mis").
+// what the fork's TODOs point at (aaportal.cpp:162 "TODO implement for MIS", the
+// commented-out MIS estimators of integrator.cpp:263-513).  The portal rectangle is sampled uniformly in
+// SOLID ANGLE as seen from the shading point (Urena, Fajardo, King: "An Area-Preserving Parametrization for
+// Spherical Rectangles", EGSR 2013), so the estimator has no distance^2 / cosine factor, and the portal is
+// picked with probability proportional to its solid angle, which the estimate IS divided by.
+struct SphRect {
+    V3 o, x, y, z;
+    float z0, x0, y0, x1, y1;
+    float b0, b1, k, S;  // S = solid angle
+};
+PG_HD float safeAcos(float v) { return acosf(clampf(v, -1.f, 1.f)); }
+// the world-space rectangle of a portal: corner and the two edge vectors
+PG_HD void portalWorldRect(const PortalRec &po, const M44 &lightO2W, V3 *corner, V3 *ex, V3 *ey) {
+    V3 lo = po.pl.lo, a = po.pl.lo, b = po.pl.lo;
+    a.set(po.pl.ax0, po.pl.hi[po.pl.ax0]);
+    b.set(po.pl.ax1, po.pl.hi[po.pl.ax1]);
+    *corner = xformPoint(lightO2W, lo);
+    *ex = xformPoint(lightO2W, a) - *corner;
+    *ey = xformPoint(lightO2W, b) - *corner;
+}
+PG_HD SphRect sphRectInit(V3 s, V3 ex, V3 ey, V3 o) {
+    SphRect q;
+    q.o = o;
+    float exl = length(ex), eyl = length(ey);
+    q.x = ex / exl;
+    q.y = ey / eyl;
+    q.z = cross(q.x, q.y);
+    V3 d = s - o;
+    q.z0 = dot(d, q.z);
+    if (q.z0 > 0) {
+        q.z = -q.z;
+        q.z0 = -q.z0;
+    }
+    q.x0 = dot(d, q.x);
+    q.y0 = dot(d, q.y);
+    q.x1 = q.x0 + exl;
+    q.y1 = q.y0 + eyl;
+    V3 v00 = v3(q.x0, q.y0, q.z0), v01 = v3(q.x0, q.y1, q.z0), v10 = v3(q.x1, q.y0, q.z0), v11 = v3(q.x1, q.y1, q.z0);
+    V3 n0 = normalize(cross(v00, v10)), n1 = normalize(cross(v10, v11)), n2 = normalize(cross(v11, v01)), n3 = normalize(cross(v01, v00));
+    float g0 = safeAcos(-dot(n0, n1)), g1 = safeAcos(-dot(n1, n2)), g2 = safeAcos(-dot(n2, n3)), g3 = safeAcos(-dot(n3, n0));
+    q.b0 = n0.z;
+    q.b1 = n2.z;
+    q.k = 2 * kPi - g2 - g3;
+    q.S = g0 + g1 - q.k;
+    if (!(q.z0 < 0) || !(q.S > 0)) q.S = 0;  // the point lies in the rectangle's plane (or numerics gave up): nothing to sample
+    return q;
+}
+PG_HD V3 sphRectSample(const SphRect &q, float u, float v) {
+    float au = u * q.S + q.k;
+    float fu = (cosf(au) * q.b0 - q.b1) / sinf(au);
+    float cu = 1 / sqrtf(fu * fu + q.b0 * q.b0) * (fu > 0 ? 1.f : -1.f);
+    cu = clampf(cu, -1.f, 1.f);
+    float xu = -(cu * q.z0) / sqrtf(maxf(1e-12f, 1 - cu * cu));
+    xu = clampf(xu, q.x0, q.x1);
+    float d = sqrtf(xu * xu + q.z0 * q.z0);
+    float h0 = q.y0 / sqrtf(d * d + q.y0 * q.y0), h1 = q.y1 / sqrtf(d * d + q.y1 * q.y1);
+    float hv = h0 + v * (h1 - h0), hv2 = hv * hv;
+    float yv = (hv2 < 1 - 1e-6f) ? (hv * d) / sqrtf(1 - hv2) : q.y1;
+    yv = clampf(yv, q.y0, q.y1);
+    return q.o + xu * q.x + yv * q.y + q.z0 * q.z;
+}
+// does the direction wi from o pass through the rectangle?
+PG_HD bool rectContainsDirection(V3 s, V3 ex, V3 ey, V3 o, V3 wi) {
+    V3 n = cross(ex, ey);
+    float denom = dot(n, wi);
+    if (denom == 0) return false;
+    float t = dot(n, s - o) / denom;
+    if (!(t > 0)) return false;
+    V3 h = o + t * wi - s;
+    float a = dot(h, ex) / dot(ex, ex), b = dot(h, ey) / dot(ey, ey);
+    return a >= 0 && a <= 1 && b >= 0 && b <= 1;
+}
+
+// Solid angles of the portals in front of p; returns their sum.  With `pick` in [0, 1): *sel = the portal drawn
+// with probability omega_i / sum and *rect = its spherical rectangle.
+PG_HD_NOINLINE float portalSolidAngles(const float *portals, int nPortals, const M44 &lightO2W, const M44 &lightW2O, V3 p, float pick, int *sel,
+                                       SphRect *rect) {
+    float sum = 0;
+    for (int i = 0; i < nPortals; ++i) {
+        PortalRec po = loadPortal(portals + PBRTGPU_PORTAL_STRIDE * i);
+        if (!portalInFront(po, lightW2O, p)) continue;
+        V3 s, ex, ey;
+        portalWorldRect(po, lightO2W, &s, &ex, &ey);
+        sum += sphRectInit(s, ex, ey, p).S;
+    }
+    *sel = -1;
+    if (!(sum > 0)) return 0;
+    float target = pick * sum, acc = 0;
+    for (int i = 0; i < nPortals; ++i) {
+        PortalRec po = loadPortal(portals + PBRTGPU_PORTAL_STRIDE * i);
+        if (!portalInFront(po, lightW2O, p)) continue;
+        V3 s, ex, ey;
+        portalWorldRect(po, lightO2W, &s, &ex, &ey);
+        SphRect q = sphRectInit(s, ex, ey, p);
+        if (!(q.S > 0)) continue;
+        *sel = i;
+        *rect = q;
+        acc += q.S;
+        if (target < acc) break;
+    }
+    return sum;
+}
+// is wi (from p) inside one of the portals in front of p?
+PG_HD bool portalsContainDirection(const float *portals, int nPortals, const M44 &lightO2W, const M44 &lightW2O, V3 p, V3 wi) {
+    for (int i = 0; i < nPortals; ++i) {
+        PortalRec po = loadPortal(portals + PBRTGPU_PORTAL_STRIDE * i);
+        if (!portalInFront(po, lightW2O, p)) continue;
+        V3 s, ex, ey;
+        portalWorldRect(po, lightO2W, &s, &ex, &ey);
+        if (rectContainsDirection(s, ex, ey, p, wi)) return true;
+    }
+    return false;
+}
+
 }  // namespace pg
 #endif

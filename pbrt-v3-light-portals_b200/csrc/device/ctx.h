@@ -63,6 +63,7 @@ struct pbrtgpu_ctx {
     bool tracePersistent = true;
     bool traceFused = true;   // one traversal launch per depth for path + next-event + shadow rays
     bool shadeSync = true;
+    bool extPortalStrategy = false;  // a portal light of the uploaded scene uses a strategy the reference does not have
     bool sortHits = true;       // hit queue split by material class (render.cu:splitHits)
     bool shadeSmemSet = false;  // k_shade_sync's shared-memory opt-in done on this device
     int shadeBlock = 5122;      // 512-thread blocks, two per SM (A/B in profiles/r01g_ab_shade.log)

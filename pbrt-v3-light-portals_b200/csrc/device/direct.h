@@ -165,6 +165,10 @@ PG_HD_NOINLINE bool estimateDirectPortalSolidAngle(const DevScene &sc, int li, i
     return true;
 }
 
+// EXT = false compiles the two non-reference strategies out: the path integrator's shade kernel is bound by
+// instruction fetch, and carrying their code costs scenes that do not use them 2 % (r01h A/B).  The host
+// launches the EXT kernel only when a light of the scene asks for one of them.
+template <bool EXT>
 PG_HD_NOINLINE void estimateDirectPortal(const DevScene &sc, int li, const SurfInt &it, const BSDF &bsdf, float u1x, float u1y,
                                 float u2x, float u2y, Spec scale, NeeRequest *out) {
     const int flagsNS = BSDF_ALL & ~BSDF_SPECULAR;
@@ -178,7 +182,7 @@ PG_HD_NOINLINE void estimateDirectPortal(const DevScene &sc, int li, const SurfI
     const float *portals = sc.portalParams + PBRTGPU_PORTAL_STRIDE * (size_t)pBegin;
     M44 w2o = loadM44(lightRec + 32);
     if (strat == PBRTGPU_PORTAL_SOLIDANGLE || strat == PBRTGPU_PORTAL_SOLIDANGLE_MIS) {
-        if (nPortals > 0 && estimateDirectPortalSolidAngle(sc, li, strat, lightRec, portals, nPortals, it, bsdf, u1x, u1y, u2x, u2y, scale, out)) return;
+        if (EXT && nPortals > 0 && estimateDirectPortalSolidAngle(sc, li, strat, lightRec, portals, nPortals, it, bsdf, u1x, u1y, u2x, u2y, scale, out)) return;
         strat = PBRTGPU_PORTAL_UNIFORM_LIGHT;  // behind every portal
     }
     if (strat != PBRTGPU_PORTAL_UNIFORM_LIGHT) {
@@ -225,7 +229,7 @@ PG_NI_DIRECT void estimateDirectRays(const DevScene &sc, int li, const SurfInt &
     *culled = false;
     int tag = PG_LD(sc.lightTag + li);
     if (tag == PBRTGPU_LIGHT_PORTAL_AREA) {
-        estimateDirectPortal(sc, li, it, bsdf, uS0, uS1, uL0, uL1, spec(1.f), out);
+        estimateDirectPortal<true>(sc, li, it, bsdf, uS0, uS1, uL0, uL1, spec(1.f), out);
         if (out->hasClosest) out->closestContrib = scale * out->closestContrib;
         return;
     }

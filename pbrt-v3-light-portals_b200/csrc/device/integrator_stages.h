@@ -99,7 +99,7 @@ struct ShadeScratch {
 };
 static_assert(sizeof(ShadeScratch) == 37 * 4, "ShadeScratch must stay an odd number of words");
 
-template <class Sync>
+template <class Sync, bool EXT = true>
 PG_HD void stageShadePhased(const WaveParams &w, int depth, int cur, int pos, bool active, Sync sync, ShadeScratch &scr) {
     const int flagsNS = BSDF_ALL & ~BSDF_SPECULAR;
     // ---- phase 0: path state, the hit record -> SurfaceInteraction, emitted light (path.cpp:91-96)
@@ -176,7 +176,7 @@ PG_HD void stageShadePhased(const WaveParams &w, int depth, int cur, int pos, bo
         r.hasShadow = r.hasClosest = false;
         r.light = -1;
         r.mode = NEE_MIS_LIGHT;
-        estimateDirectPortal(w.sc, li, it, bsdf, uS0, uS1, uL0, uL1, spec(1.f), &r);
+        estimateDirectPortal<EXT>(w.sc, li, it, bsdf, uS0, uS1, uL0, uL1, spec(1.f), &r);
         if (r.hasClosest) {
             Spec c = beta * (r.closestContrib / pickPdf);
             int np = atomicIncInt(&w.cnt->nNee[depth]);

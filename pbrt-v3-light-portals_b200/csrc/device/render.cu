@@ -211,7 +211,7 @@ __global__ void __launch_bounds__(kStageBlock) k_shade(const WaveParams *__restr
 struct BlockSync {
     __device__ __forceinline__ void operator()() const { __syncthreads(); }
 };
-template <int BLOCK, int PER_SM>
+template <int BLOCK, int PER_SM, bool EXT = false>  // EXT: with the non-reference portal strategies (direct.h)
 __global__ void __launch_bounds__(BLOCK, PER_SM) k_shade_sync(const WaveParams *__restrict__ wp, int depth, int cur) {
     const WaveParams &w = *wp;
     int n = hitQueueLen(w, depth);
@@ -225,7 +225,7 @@ __global__ void __launch_bounds__(BLOCK, PER_SM) k_shade_sync(const WaveParams *
     for (int base = blockIdx.x * blockDim.x; base < n; base += stride) {
         int i = base + threadIdx.x;
         bool active = i < n;
-        stageShadePhased(w, depth, cur, active ? hitQueueAt(w, depth, i) : 0, active, BlockSync(), scr);
+        stageShadePhased<BlockSync, EXT>(w, depth, cur, active ? hitQueueAt(w, depth, i) : 0, active, BlockSync(), scr);
     }
 }
 

@@ -180,6 +180,9 @@ int pbrtgpu_upload_scene(pbrtgpu_ctx *ctx, const pbrtgpu_scene *s) {
     UP(s->light_tag, s->n_lights, &d.lightTag);
     UP(s->light_prim, s->n_lights, &d.lightPrim);
     UP(s->light_strategy, s->n_lights, &d.lightStrategy);
+    ctx->extPortalStrategy = false;
+    for (int i = 0; i < s->n_lights; ++i)
+        if (s->light_tag[i] == PBRTGPU_LIGHT_PORTAL_AREA && s->light_strategy && s->light_strategy[i] >= PBRTGPU_PORTAL_SOLIDANGLE) ctx->extPortalStrategy = true;
     {
         std::vector<MatLobes> lobes;
         buildMaterialLobes(s, &lobes);

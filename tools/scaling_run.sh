@@ -1,10 +1,12 @@
 #!/bin/bash
-# bench.py at N = 1, 2, 4, 8 GPUs of one box, launched the way the driver does (torchrun for N > 1).
-# usage (on the GPU box): tools/scaling_run.sh [outfile]   -> one JSON line per N
+# bench.py at N = 1, 2, 4, 8 GPUs of one box (or the Ns given), launched the way the driver does (torchrun for N > 1).
+# usage (on the GPU box): tools/scaling_run.sh outfile [N ...]   -> one JSON line per N
 out=${1:-gpurun_out/scaling.jsonl}
+shift
+ns=${@:-1 2 4 8}
 mkdir -p "$(dirname "$out")"
 : > "$out"
-for n in 1 2 4 8; do
+for n in $ns; do
   if [ "$n" = 1 ]; then
     python bench.py --gpus 1 --steps 8 --warmup 3 --no-cpu-baseline 2>>"$out.err" | grep '^{' >> "$out"
   else

@@ -540,10 +540,7 @@ PG_HD void stageFilm(const WaveParams &w, int slot) {
             float *px = fp.rgbw + 4 * ((size_t)(y - fp.cropped[1]) * width + (x - fp.cropped[0]));
             // pixel.contribSum += L * sampleWeight * filterWeight; sampleWeight (the camera ray weight) is 1
             Spec c = L * 1.f * fw;
-            atomicAddFloat(px + 0, c.r);
-            atomicAddFloat(px + 1, c.g);
-            atomicAddFloat(px + 2, c.b);
-            atomicAddFloat(px + 3, fw);
+            atomicAddFloat4(px, c.r, c.g, c.b, fw);
         }
     }
 }

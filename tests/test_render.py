@@ -273,6 +273,27 @@ def test_gpu_shards_add_up(pkg, gpu, golden):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("knob", ["PBRTGPU_SORT_HITS=0", "PBRTGPU_SHADE_BLOCK=1024", "PBRTGPU_SHADE_SYNC=0"])
+def test_gpu_scheduling_knobs_do_not_change_the_image(pkg, gpu, monkeypatch, knob):
+    """How vertices are mapped to threads -- the hit queue split by material class, the shade block shape, phase
+    barriers or none -- must not change any path: only the order of float atomics into a film pixel may differ."""
+    hs = load_case(pkg, "box_glass")  # matte + plastic + glass: both material classes in one image
+    gpu.upload(hs)
+    film, _ = gpu.render(hs.params)
+    a = hs.film_to_rgb(film)
+    k, v = knob.split("=")
+    monkeypatch.setenv(k, v)
+    ctx = pkg.GpuContext(0)  # the knobs are read when a context is created
+    try:
+        ctx.upload(hs)
+        film, _ = ctx.render(hs.params)
+    finally:
+        ctx.close()
+    s = util.image_stats(hs.film_to_rgb(film), a)
+    assert s["rel_rmse"] <= 1e-5, (knob, s)
+
+
+@pytest.mark.gpu
 def test_gpu_render_errors(pkg, gpu):
     hs = load_case(pkg, "tri_soup")
     gpu.upload(hs)

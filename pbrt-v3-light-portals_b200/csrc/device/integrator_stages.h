@@ -84,7 +84,7 @@ PG_HD void stageMiss(const WaveParams &w, int depth, int cur, int pos) {
 // serve them all.  Every thread of the block calls this function, `active`
 // or not.  On the CPU (tests/hostsim) sync() does nothing.
 struct NoSync {
-    PG_HD void operator()() const {}
+    PG_HD void operator()(int) const {}
 };
 
 // The two records that live across all phases and are handed by reference to the out-of-line leaves.  On the
@@ -132,7 +132,7 @@ PG_HD void stageShadePhased(const WaveParams &w, int depth, int cur, int pos, bo
         if (mat < 0) next = spawnRay(it.p, it.pError, it.n, ray.d);
     }
     const bool scatter = alive && mat >= 0;
-    sync();
+    sync(0);
 
     // ---- phase 1: the material's BSDF (path.cpp:106-107)
     PathSampler smp;
@@ -144,7 +144,7 @@ PG_HD void stageShadePhased(const WaveParams &w, int depth, int cur, int pos, bo
         smp.dim = w.dim[slot];
         makeBSDF(it, w.sc.matLobes, mat, w.sc.matParams + PBRTGPU_MAT_STRIDE * (size_t)mat, wvl0, &bsdf);
     }
-    sync();
+    sync(1);
 
     // ---- phase 2: UniformSampleOneLight's samples and light pick (integrator.cpp:100-122)
     bool nee = scatter && bsdfNumComponents(bsdf, flagsNS) > 0 && w.sc.nLights > 0;
@@ -161,7 +161,7 @@ PG_HD void stageShadePhased(const WaveParams &w, int depth, int cur, int pos, bo
         get2D(w.hal, smp, &uS0, &uS1);
         lightTag = PG_LD(w.sc.lightTag + li);
     }
-    sync();
+    sync(2);
 
     // ---- phase 3: sample the light (EstimateDirect, integrator.cpp:133-141); portal lights take their own estimator
     const bool portal = nee && lightTag == PBRTGPU_LIGHT_PORTAL_AREA;
@@ -187,7 +187,7 @@ PG_HD void stageShadePhased(const WaveParams &w, int depth, int cur, int pos, bo
         }
     }
     if (stock) Li = lightSampleLi(w.sc, li, it, uL0, uL1, &wi, &lightPdf, &pL);
-    sync();
+    sync(3);
 
     // ---- phase 4: BSDF value and pdf for the light sample; the shadow ray (integrator.cpp:142-184)
     if (stock && lightPdf > 0 && !isBlack(Li)) {
@@ -204,7 +204,7 @@ PG_HD void stageShadePhased(const WaveParams &w, int depth, int cur, int pos, bo
             w.shadowContrib[sp] = f4(c.r, c.g, c.b, bitsToFloat((unsigned)slot));
         }
     }
-    sync();
+    sync(4);
 
     // ---- phase 5: sample the BSDF for MIS (integrator.cpp:187-207)
     bool misRay = stock && !isDelta;
@@ -217,7 +217,7 @@ PG_HD void stageShadePhased(const WaveParams &w, int depth, int cur, int pos, bo
         sampledSpecular = (sampledType & BSDF_SPECULAR) != 0;
         misRay = !isBlack(fMis) && scatteringPdf > 0;
     }
-    sync();
+    sync(5);
 
     // ---- phase 6: the light's pdf for that direction; the MIS ray (integrator.cpp:208-254)
     if (misRay) {
@@ -245,7 +245,7 @@ PG_HD void stageShadePhased(const WaveParams &w, int depth, int cur, int pos, bo
             w.neeInfo[2 * (size_t)np + 1] = NEE_MIS_LIGHT;
         }
     }
-    sync();
+    sync(6);
 
     // ---- phase 7: sample the BSDF for the next direction (path.cpp:131-151)
     V3 wo = v3(0, 0, 0);
@@ -259,7 +259,7 @@ PG_HD void stageShadePhased(const WaveParams &w, int depth, int cur, int pos, bo
         get2D(w.hal, smp, &u0, &u1);
         f = bsdfSampleF(bsdf, wo, &wi, u0, u1, &pdf, BSDF_ALL, &sampled);
     }
-    sync();
+    sync(7);
 
     // ---- phase 8: throughput, Russian roulette (path.cpp:177-184), the next ray
     if (scatter) {

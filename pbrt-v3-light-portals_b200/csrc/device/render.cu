@@ -208,8 +208,14 @@ __global__ void __launch_bounds__(kStageBlock) k_shade(const WaveParams *__restr
 
 // One 384-thread block per SM, all of whose warps walk the phases of stageShadePhased together
 // (__syncthreads between phases): the shading code is far larger than the instruction cache.
+#ifndef PG_SYNC_MASK
+#define PG_SYNC_MASK 0xff
+#endif
 struct BlockSync {
-    __device__ __forceinline__ void operator()() const { __syncthreads(); }
+    // i = the phase that just ended; PG_SYNC_MASK (A/B builds) drops individual barriers
+    __device__ __forceinline__ void operator()(int i) const {
+        if ((PG_SYNC_MASK >> i) & 1) __syncthreads();
+    }
 };
 template <int BLOCK, int PER_SM, bool EXT = false>  // EXT: with the non-reference portal strategies (direct.h)
 __global__ void __launch_bounds__(BLOCK, PER_SM) k_shade_sync(const WaveParams *__restrict__ wp, int depth, int cur) {

@@ -80,19 +80,22 @@ inline BatchPlan planBatches(const pbrtgpu_render_params *rp, long long targetSl
     p.sppEnd = rp->spp_end > rp->spp_begin ? rp->spp_end : rp->spp;
     int spp = p.sppEnd - p.sppBegin;
     p.sppChunk = spp < 32 ? (spp > 0 ? spp : 1) : 32;
+    bool wholeShard = false;  // every batch takes all of the shard's tiles
     // Few tiles (one shard of many, a small image): take more sample numbers of every pixel into a batch, so that it
     // still fills targetSlots -- half-size batches pay the tail of every traversal launch twice (8 GPUs: 4 batches
     // of 8 M slots per step instead of 2 of 16 M cost 2 ms of 48).  The sample numbers are split evenly.
     if (p.shardTiles > 0 && spp > 32) {
         long long want = targetSlots / (256LL * p.shardTiles);
         if (want > 32) {
-            int nChunks = (int)((spp + want - 1) / want);
+            long long most = want + want / 4;  // a batch may exceed the target by a quarter rather than leave a small remainder
+            int nChunks = (int)((spp + most - 1) / most);
             p.sppChunk = (spp + nChunks - 1) / nChunks;
+            wholeShard = true;
         }
     }
     long long t = targetSlots / (256LL * p.sppChunk);
     if (t < 1) t = 1;
-    if (t > p.shardTiles) t = p.shardTiles > 0 ? p.shardTiles : 1;
+    if (t > p.shardTiles || wholeShard) t = p.shardTiles > 0 ? p.shardTiles : 1;
     p.tilesPerBatch = (int)t;
     p.maxSlots = p.tilesPerBatch * 256 * p.sppChunk;
     // a path makes at most maxDepth + 1 scene intersections; vertices on

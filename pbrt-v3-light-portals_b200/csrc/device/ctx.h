@@ -63,6 +63,7 @@ struct pbrtgpu_ctx {
     bool tracePersistent = true;
     bool traceFused = true;   // one traversal launch per depth for path + next-event + shadow rays
     bool shadeSync = true;
+    int lightStageBlocksPerSM = 16;  // grid of k_split_hits / k_post_trace, in 128-thread blocks per SM
     bool extPortalStrategy = false;  // a portal light of the uploaded scene uses a strategy the reference does not have
     bool sortHits = true;       // hit queue split by material class (render.cu:splitHits)
     bool shadeSmemSet = false;  // k_shade_sync's shared-memory opt-in done on this device

@@ -73,6 +73,7 @@ int pbrtgpu_create(int cuda_device, pbrtgpu_ctx **out) {
     if (const char *v = getenv("PBRTGPU_TRACE_PERSISTENT")) ctx->tracePersistent = atoi(v) != 0;
     if (const char *v = getenv("PBRTGPU_TRACE_FUSED")) ctx->traceFused = atoi(v) != 0;
     if (const char *v = getenv("PBRTGPU_SHADE_SYNC")) ctx->shadeSync = atoi(v) != 0;
+    if (const char *v = getenv("PBRTGPU_LIGHT_STAGE_BLOCKS")) ctx->lightStageBlocksPerSM = std::min(32, std::max(1, atoi(v)));
     if (const char *v = getenv("PBRTGPU_SORT_HITS")) ctx->sortHits = atoi(v) != 0;
     if (const char *v = getenv("PBRTGPU_FETCH_THRESHOLD")) ctx->fetchThreshold = std::min(32, std::max(1, atoi(v)));
     if (const char *v = getenv("PBRTGPU_SHADE_BLOCK")) ctx->shadeBlock = atoi(v);

@@ -322,7 +322,7 @@ def main():
            "config": {"workload": scene_desc + ", %dx%d" % RES + ", Integrator path maxdepth 5, halton; one step = %d spp of the full frame per GPU "
                       "(sample numbers of the %d-spp job), 16x16 tiles sharded over ranks, film reduce per step" % (S, TOTAL_SPP),
                       "spp_per_step_per_gpu": S, "l2": "wavefront state of a step (%.0f MB) and the film exceed L2; no flush needed" %
-                      (min(samples_per_step // world, 16 << 20) * 290 / 1e6), "rays_per_sample": float(tot[1].item()) / (samples_per_step * args.steps)},
+                      (min(samples_per_step // world, 64 << 20) * 290 / 1e6), "rays_per_sample": float(tot[1].item()) / (samples_per_step * args.steps)},
            "gpu_launches": int(tot[0].item()), "clocks": clk,
            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(scene_bytes), "d2h_bytes_per_step": int(n_pix * 16), "steps": e2e_steps, "step_ms": e2e_step_ms},
            "roofline": roofline}

@@ -71,7 +71,7 @@ def build_gpu(verbose=False):
         nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
         extra = os.environ.get("PBRTGPU_EXTRA_NVCC_FLAGS", "").split()  # tuning experiments, e.g. -DPG_PERSIST_MIN_BLOCKS=8
         log = _run([nvcc] + NVCC_FLAGS + extra + ["-Xptxas", "-v", "-shared", "-I" + os.path.join(ROOT, "include")] + srcs +
-                   ["-o", target, "-lcudart"])
+                   ["-o", target, "-lcudart", "-lpthread"])
         with open(os.path.join(OUT, "ptxas.log"), "w") as f:
             f.write(log)
         if verbose:

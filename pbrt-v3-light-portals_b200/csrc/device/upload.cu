@@ -3,6 +3,7 @@
 #include <algorithm>
 #include <cstdlib>
 #include <cstring>
+#include <thread>
 #include <vector>
 
 #include "../common/halton_tables.h"
@@ -151,12 +152,15 @@ int pbrtgpu_upload_scene(pbrtgpu_ctx *ctx, const pbrtgpu_scene *s) {
     DevScene &d = ctx->scene;
     memset(&d, 0, sizeof(d));
 
-    std::vector<F4> wide;
-    buildWideNodes(s, &wide);
-    std::vector<F4> tris;
+    // the two layout conversions are independent: primitives on a second thread while this one does the nodes
+    std::vector<F4> wide, tris;
     {
         std::string err;
-        if (!buildTris(s, &tris, &err)) return ctx->fail(PBRTGPU_ERR_INVALID, "%s", err.c_str());
+        bool trisOk = true;
+        std::thread trisThread([&] { trisOk = buildTris(s, &tris, &err); });
+        buildWideNodes(s, &wide);
+        trisThread.join();
+        if (!trisOk) return ctx->fail(PBRTGPU_ERR_INVALID, "%s", err.c_str());
     }
 
     int rc;

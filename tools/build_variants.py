@@ -24,7 +24,7 @@ def main():
         name, flags = arg.split("=", 1)
         target = os.path.join(out, "libpbrtgpu_%s.so" % name)
         log = b._run(["nvcc"] + b.NVCC_FLAGS + flags.split() + ["-Xptxas", "-v", "-shared", "-I" + os.path.join(ROOT, "include")] + srcs +
-                     ["-o", target, "-lcudart"])
+                     ["-o", target, "-lcudart", "-lpthread"])
         m = re.search(r"k_shade_syncILi1024ELi1.*?\n.*?\n\s*(\d+) bytes stack frame, (\d+) bytes spill stores, (\d+) bytes spill loads", log)
         print(name, "->", target, "shade<1024>: stack %s spill st %s ld %s" % m.groups() if m else "")
 

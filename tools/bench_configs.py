@@ -2,7 +2,7 @@
 (run on the GPU box).  Prints one JSON line per configuration.
 
   C1  scenes/cornell_dielectric.pbrt, Integrator "path" maxdepth 5, 64 spp (512x512, gaussian filter)
-  C3  tests/scenes/portal_room.pbrt at 512x512, 64 spp, strategy light | portal | projection
+  C3  tests/scenes/portal_room.pbrt at 512x512, 64 spp, strategy light | portal | projection | solidangle | solidangle_mis
   C5  100 M closest-hit and any-hit rays against the killeroo BVH (tools/bench_rays.py covers this one)
 """
 import importlib, json, os, re, sys
@@ -42,6 +42,6 @@ if __name__ == "__main__":
         t2 = re.sub(r'PixelFilter\s+"gaussian"\s+"float xwidth"\s*\[2\]\s+"float ywidth"\s*\[2\]', 'PixelFilter "box"', bench.scene_variant(p, 256, (1024, 1024)))
         run("C1 variant: box filter, 1024x1024 256spp", t2, ref_scenes)
     room = os.path.join(ROOT, "tests", "scenes", "portal_room.pbrt")
-    for s in ("light", "portal", "projection"):
+    for s in ("light", "portal", "projection", "solidangle", "solidangle_mis"):  # the last two are not the reference's
         t = bench.scene_variant(room, 64, (512, 512)).replace("STRATEGY", s).replace('"integer maxdepth" [4]', '"integer maxdepth" [5]')
         run("C3 portal room 512x512 64spp strategy " + s, t, os.path.dirname(room))

@@ -25,6 +25,7 @@ struct HaltonParams {
     int baseScales[2], baseExponents[2];
     int sampleStride;
     int multInverse[2];
+    int pixelOffsetMul[2];         // ((sampleStride / baseScales[i]) * multInverse[i]) mod sampleStride
     int sampleAtPixelCenter;
     int arrayEndDim;               // GlobalSampler: dimensions [kArrayStartDim, arrayEndDim) hold the sample arrays (sampler.cpp:126-148)
     const int *primes;             // 1000 entries
@@ -52,10 +53,12 @@ PG_HD long long haltonPixelOffset(const HaltonParams &h, int px, int py) {
                 inverse /= base;
                 index = index * base + digit;
             }
-            offset += (unsigned long long)index * (unsigned long long)(h.sampleStride / h.baseScales[i]) *
-                      (unsigned long long)h.multInverse[i];
+            // halton.cpp:110-112 adds index * (stride / scale_i) * multInverse_i and reduces mod stride at the end; the
+            // factor is reduced mod stride beforehand (makeHaltonParams), which leaves the residue unchanged and keeps
+            // every product below 2^32 -- a 32-bit remainder per sample instead of two divisions and a 64-bit one.
+            offset += (unsigned long long)(index * (unsigned)h.pixelOffsetMul[i]);
         }
-        offset %= (unsigned long long)h.sampleStride;
+        offset = (unsigned long long)((unsigned)offset % (unsigned)h.sampleStride);
     }
     return (long long)offset;
 }
@@ -217,6 +220,9 @@ inline HaltonParams makeHaltonParams(const int sampleBounds[4], int sampleAtPixe
         long long m = x - (x / n) * n;  // Mod(x, n)
         h.multInverse[i] = (int)(m < 0 ? m + n : m);
     }
+    for (int i = 0; i < 2; ++i)
+        h.pixelOffsetMul[i] = (int)(((unsigned long long)(h.sampleStride / h.baseScales[i]) * (unsigned long long)h.multInverse[i]) %
+                                    (unsigned long long)h.sampleStride);
     h.sampleAtPixelCenter = sampleAtPixelCenter;
     h.arrayEndDim = kArrayStartDim;  // no sample arrays requested
     h.primes = nullptr;

@@ -76,14 +76,21 @@ struct CameraSample {
 };
 
 // GetCameraSample: 6 dimensions, in this order.
-PG_HD CameraSample getCameraSample(const HaltonParams &h, PathSampler &s, int px, int py) {
+// needTimeAndLens = false: the camera is a pinhole and nothing moves, so the time and lens samples (dimensions
+// 2, 3, 4) have no reader; the sampler's dimension still advances past them, their values are not computed.
+PG_HD CameraSample getCameraSample(const HaltonParams &h, PathSampler &s, int px, int py, bool needTimeAndLens = true) {
     CameraSample cs;
     float u0, u1;
     get2D(h, s, &u0, &u1);
     cs.pFilmX = (float)px + u0;
     cs.pFilmY = (float)py + u1;
-    cs.time = get1D(h, s);
-    get2D(h, s, &cs.pLensX, &cs.pLensY);
+    if (needTimeAndLens) {
+        cs.time = get1D(h, s);
+        get2D(h, s, &cs.pLensX, &cs.pLensY);
+    } else {
+        cs.time = cs.pLensX = cs.pLensY = 0;
+        s.dim += 3;  // dimensions 2..4 lie below GlobalSampler's array dimensions: no jump to account for
+    }
     cs.wvl = get1D(h, s);
     return cs;
 }

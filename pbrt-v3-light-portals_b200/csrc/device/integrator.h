@@ -156,7 +156,7 @@ PG_HD void stageRaygen(const WaveParams &w, int slot) {
     PathSampler smp;
     smp.index = haltonPixelOffset(w.hal, px, py) + (long long)sampleNum * w.hal.sampleStride;
     smp.dim = 0;
-    CameraSample cs = getCameraSample(w.hal, smp, px, py);
+    CameraSample cs = getCameraSample(w.hal, smp, px, py, w.cam.lensRadius > 0);
     float wvl0;
     Ray ray = generateCameraRay(w.cam, cs, &wvl0);
     w.hIndex[slot] = smp.index;

@@ -78,7 +78,8 @@ struct CameraSample {
 // GetCameraSample: 6 dimensions, in this order.
 // needTimeAndLens = false: the camera is a pinhole and nothing moves, so the time and lens samples (dimensions
 // 2, 3, 4) have no reader; the sampler's dimension still advances past them, their values are not computed.
-PG_HD CameraSample getCameraSample(const HaltonParams &h, PathSampler &s, int px, int py, bool needTimeAndLens = true) {
+// needWavelength = false: no material of the scene is dispersive, so the hero wavelength (dimension 5) has no reader either.
+PG_HD CameraSample getCameraSample(const HaltonParams &h, PathSampler &s, int px, int py, bool needTimeAndLens = true, bool needWavelength = true) {
     CameraSample cs;
     float u0, u1;
     get2D(h, s, &u0, &u1);
@@ -91,7 +92,12 @@ PG_HD CameraSample getCameraSample(const HaltonParams &h, PathSampler &s, int px
         cs.time = cs.pLensX = cs.pLensY = 0;
         s.dim += 3;  // dimensions 2..4 lie below GlobalSampler's array dimensions: no jump to account for
     }
-    cs.wvl = get1D(h, s);
+    if (needWavelength) cs.wvl = get1D(h, s);
+    else {
+        if (s.dim >= kArrayStartDim && s.dim < h.arrayEndDim) s.dim = h.arrayEndDim;  // GlobalSampler::Get1D's jump over the sample arrays
+        ++s.dim;
+        cs.wvl = 0;
+    }
     return cs;
 }
 

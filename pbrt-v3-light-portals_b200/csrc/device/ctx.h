@@ -54,6 +54,7 @@ struct pbrtgpu_ctx {
     bool specTransDispersive = false;
     long long sumLightSamples = 0;                  // sum of Light::nSamples (directlighting "all")
     bool hasInfiniteLight = false;
+    bool hasDispersiveMaterial = false;             // some material's index of refraction follows the path's wavelength
     bool hasNullMaterial = false;                   // some primitive has no material (path.cpp:108-113)
     // render scratch, grown on demand
     pg::DeviceBuffer scratch[16];

@@ -76,6 +76,7 @@ struct WaveParams {
     F4 *neeHits;
     unsigned char *shadowOcc;
     WaveCounters *cnt;
+    int skipWavelength;    // no dispersive material: the camera sample's wavelength dimension is stepped over, not computed
     int sortHits;          // split the hit queue by material class (single-lobe / multi-lobe) so that a warp shades one class
     int phaseBias;         // persistent trace kernels: box-test rounds vs primitive-test rounds, see trace_persistent.h
     int fetchThreshold;    // persistent trace kernels refill a warp when this many lanes are idle
@@ -156,7 +157,7 @@ PG_HD void stageRaygen(const WaveParams &w, int slot) {
     PathSampler smp;
     smp.index = haltonPixelOffset(w.hal, px, py) + (long long)sampleNum * w.hal.sampleStride;
     smp.dim = 0;
-    CameraSample cs = getCameraSample(w.hal, smp, px, py, w.cam.lensRadius > 0);
+    CameraSample cs = getCameraSample(w.hal, smp, px, py, w.cam.lensRadius > 0, !w.skipWavelength);
     float wvl0;
     Ray ray = generateCameraRay(w.cam, cs, &wvl0);
     w.hIndex[slot] = smp.index;

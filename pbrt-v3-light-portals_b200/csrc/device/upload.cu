@@ -192,6 +192,9 @@ int pbrtgpu_upload_scene(pbrtgpu_ctx *ctx, const pbrtgpu_scene *s) {
         std::vector<MatLobes> lobes;
         buildMaterialLobes(s, &lobes);
         UP(lobes.data(), lobes.size(), &d.matLobes);
+        ctx->hasDispersiveMaterial = false;
+        for (const MatLobes &m : lobes)
+            if (m.dispersive) ctx->hasDispersiveMaterial = true;
         ctx->maxSpecTransLobes = maxSpecularTransmissionLobes(lobes, s->n_materials, &ctx->specTransDispersive);
     }
     UP(s->light_portal_begin, s->light_portal_begin ? s->n_lights + 1 : 0, &d.lightPortalBegin);

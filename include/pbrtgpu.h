@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define PBRTGPU_ABI_VERSION 2
+#define PBRTGPU_ABI_VERSION 3
 
 typedef enum {
     PBRTGPU_OK = 0,
@@ -172,6 +172,10 @@ typedef struct {
     float device_ms;        /* CUDA-event time of the render, device only */
     int64_t nee_rays_culled; /* BSDF-sampled MIS rays the reference would trace but which miss the sampled light's own shape:
                                 their closest hit cannot be that light, they contribute nothing and are not traced (not in closest_rays) */
+    int64_t truncated_paths; /* paths still alive when an open-ended batch reached its iteration cap (a chain of more than ~4000
+                                material-less boundaries or pending branches); their radiance so far is splatted.  0 in every parity test */
+    int64_t nee_rays_dropped; /* light-sample rays that found their queue full (cannot happen while the queue is sized
+                                 nSlots x light samples per vertex; counted so that it can never be a silent bias).  Must be 0 */
 } pbrtgpu_stats;
 
 /* Kernels of the wavefront, for per-kernel timing (pbrtgpu_profile). */

@@ -79,7 +79,8 @@ class RenderParams(C.Structure):  # pbrtgpu_render_params
 
 class Stats(C.Structure):  # pbrtgpu_stats
     _fields_ = [("camera_rays", C.c_int64), ("closest_rays", C.c_int64), ("shadow_rays", C.c_int64),
-                ("scrubbed", C.c_int64), ("kernel_launches", C.c_int64), ("nee_closest_rays", C.c_int64), ("device_ms", C.c_float), ("nee_rays_culled", C.c_int64)]
+                ("scrubbed", C.c_int64), ("kernel_launches", C.c_int64), ("nee_closest_rays", C.c_int64), ("device_ms", C.c_float), ("nee_rays_culled", C.c_int64),
+                ("truncated_paths", C.c_int64), ("nee_rays_dropped", C.c_int64)]
 
 
 K_NAMES = ["raygen", "trace_closest", "shade", "trace_shadow", "trace_nee", "film"]

@@ -25,6 +25,7 @@ struct WaveCounters {
     int fetch[3][kMaxDepthSlots];     // persistent trace kernels: next unclaimed queue position {closest, shadow, nee}
     int nNeeCulled[kMaxDepthSlots];   // MIS rays not traced because they miss the sampled light's shape (bvh.h:primitiveAccepts)
     unsigned long long cameraRays, closestRays, shadowRays, scrubbed;
+    unsigned long long dropped;       // light-sample rays that found their queue full (pushDirectRays); must stay 0
 };
 
 struct FilmParams {

@@ -310,7 +310,8 @@ PG_HD void pushDirectRays(const WaveParams &w, int depth, int slot, const NeeReq
         if (sp < w.neeCapacity) {
             storeRay(w.shadowRays, sp, r.shadowRay);
             w.shadowContrib[sp] = f4(r.shadowContrib.r, r.shadowContrib.g, r.shadowContrib.b, bitsToFloat((unsigned)slot));
-        }
+        } else
+            atomicAddU64(&w.cnt->dropped, 1ull);  // never with queues of nSlots x light samples per vertex; reported, not silent
     }
     if (r.hasClosest) {
         int np = atomicIncInt(&w.cnt->nNee[depth]);
@@ -319,7 +320,8 @@ PG_HD void pushDirectRays(const WaveParams &w, int depth, int slot, const NeeReq
             w.neeContrib[np] = f4(r.closestContrib.r, r.closestContrib.g, r.closestContrib.b, bitsToFloat((unsigned)slot));
             w.neeInfo[2 * (size_t)np] = r.light;
             w.neeInfo[2 * (size_t)np + 1] = r.mode;
-        }
+        } else
+            atomicAddU64(&w.cnt->dropped, 1ull);
     }
 }
 

@@ -113,10 +113,15 @@ struct FusedQueue {
     }
 };
 
+// Lengths of the light-sample queues as their consumers see them: a push past the capacity is counted
+// (WaveCounters::dropped) and not stored, so the counter can exceed what the queue holds.
+__device__ __forceinline__ int neeQueueLen(const WaveParams &w, int depth) { return min(w.cnt->nNee[depth], w.neeCapacity); }
+__device__ __forceinline__ int shadowQueueLen(const WaveParams &w, int depth) { return min(w.cnt->nShadow[depth], w.neeCapacity); }
+
 template <bool COUNT>
 __global__ void __launch_bounds__(kTraceBlock, kPersistMinBlocks) k_ptrace_fused(WaveParams w, int depth, int cur) {
     TraverseCounters c[3] = {{0, 0}, {0, 0}, {0, 0}};
-    const int nPath = w.cnt->nActive[depth + 1], nNee = w.cnt->nNee[depth], nShadow = w.cnt->nShadow[depth];
+    const int nPath = w.cnt->nActive[depth + 1], nNee = neeQueueLen(w, depth), nShadow = shadowQueueLen(w, depth);
     FusedQueue q = {w.rays[cur ^ 1], w.neeRays, w.shadowRays, nPath, nNee};
     tracePersistent<kTraceMixed, COUNT>(w.sc.bvh, q, nPath + nNee + nShadow, &w.cnt->fetch[1][depth], w.fetchThreshold, w.phaseBias, c,
                                         [&](int i, int kind, const Ray &, const Hit &h, bool found) {
@@ -161,7 +166,7 @@ __global__ void __launch_bounds__(kStageBlock) k_split_hits(WaveParams w, int de
 // after k_ptrace_fused(depth): the light samples of this depth count where unoccluded, and the
 // next depth's queue is split into hits and misses
 __global__ void __launch_bounds__(kStageBlock) k_post_trace(WaveParams w, int depth, bool wantMiss) {
-    int nS = w.cnt->nShadow[depth], nA = w.cnt->nActive[depth + 1];
+    int nS = shadowQueueLen(w, depth), nA = w.cnt->nActive[depth + 1];
     int stride = gridDim.x * blockDim.x;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < nS; i += stride) stageShadowResolve(w, i, w.shadowOcc[i] != 0);
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < nA; i += stride) splitHits(w, depth + 1, wantMiss, i);
@@ -170,13 +175,13 @@ __global__ void __launch_bounds__(kStageBlock) k_post_trace(WaveParams w, int de
 template <bool COUNT>
 __global__ void __launch_bounds__(kTraceBlock, kPersistMinBlocks) k_ptrace_shadow(WaveParams w, int depth) {
     TraverseCounters c = {0, 0};
-    tracePersistent<kTraceAny, COUNT>(w.sc.bvh, SingleQueue{w.shadowRays, 1}, w.cnt->nShadow[depth], &w.cnt->fetch[1][depth], w.fetchThreshold,
+    tracePersistent<kTraceAny, COUNT>(w.sc.bvh, SingleQueue{w.shadowRays, 1}, shadowQueueLen(w, depth), &w.cnt->fetch[1][depth], w.fetchThreshold,
                                       w.phaseBias, &c, [&](int i, int, const Ray &, const Hit &, bool occluded) { w.shadowOcc[i] = occluded ? 1 : 0; });
     flushCounts<COUNT>(w, 1, c);
 }
 
 __global__ void __launch_bounds__(kStageBlock) k_shadow_resolve(WaveParams w, int depth) {
-    int n = w.cnt->nShadow[depth];
+    int n = shadowQueueLen(w, depth);
     int stride = gridDim.x * blockDim.x;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) stageShadowResolve(w, i, w.shadowOcc[i] != 0);
 }
@@ -184,7 +189,7 @@ __global__ void __launch_bounds__(kStageBlock) k_shadow_resolve(WaveParams w, in
 template <bool COUNT>
 __global__ void __launch_bounds__(kTraceBlock, kPersistMinBlocks) k_ptrace_nee(WaveParams w, int depth) {
     TraverseCounters c = {0, 0};
-    tracePersistent<kTraceClosest, COUNT>(w.sc.bvh, SingleQueue{w.neeRays, 0}, w.cnt->nNee[depth], &w.cnt->fetch[2][depth], w.fetchThreshold,
+    tracePersistent<kTraceClosest, COUNT>(w.sc.bvh, SingleQueue{w.neeRays, 0}, neeQueueLen(w, depth), &w.cnt->fetch[2][depth], w.fetchThreshold,
                                           w.phaseBias, &c, [&](int i, int, const Ray &, const Hit &h, bool) {
                                               w.neeHits[i] = f4(__int_as_float(h.prim), h.b0, h.b1, h.b2);
                                           });
@@ -194,7 +199,7 @@ __global__ void __launch_bounds__(kTraceBlock, kPersistMinBlocks) k_ptrace_nee(W
 // the emitter lookup / MIS weight of the rays k_ptrace_nee traced
 __global__ void __launch_bounds__(kStageBlock) k_nee_resolve(const WaveParams *__restrict__ wp, int depth) {
     const WaveParams &w = *wp;
-    int n = w.cnt->nNee[depth];
+    int n = neeQueueLen(w, depth);
     int stride = gridDim.x * blockDim.x;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) stageNeeResolve(w, i);
 }
@@ -256,7 +261,7 @@ __global__ void __launch_bounds__(kStageBlock) k_miss(WaveParams w, int depth, i
 
 template <bool COUNT>
 __global__ void __launch_bounds__(kTraceBlock) k_trace_shadow(WaveParams w, int depth) {
-    int n = w.cnt->nShadow[depth];
+    int n = shadowQueueLen(w, depth);
     int stride = gridDim.x * blockDim.x;
     TraverseCounters c = {0, 0};
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
@@ -269,7 +274,7 @@ __global__ void __launch_bounds__(kTraceBlock) k_trace_shadow(WaveParams w, int 
 
 template <bool COUNT>
 __global__ void __launch_bounds__(kTraceBlock) k_trace_nee(WaveParams w, int depth) {
-    int n = w.cnt->nNee[depth];
+    int n = neeQueueLen(w, depth);
     int stride = gridDim.x * blockDim.x;
     TraverseCounters c = {0, 0};
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
@@ -302,12 +307,14 @@ __global__ void k_batch_stats(WaveCounters *cnt, unsigned long long *totals, int
     totals[4] += nee;
     totals[2] += shadow;
     totals[3] += cnt->scrubbed;
+    totals[6] += cnt->dropped;
     const int a = cnt->nActive[depths], h = depths < kMaxDepthSlots ? cnt->nHit[depths] : 0, m = depths < kMaxDepthSlots ? cnt->nMiss[depths] : 0;
     const int hb = depths < kMaxDepthSlots ? cnt->nHitB[depths] : 0;
     for (int d = 0; d <= kMaxDepthSlots; ++d) cnt->nActive[d] = 0;
     for (int d = 0; d < kMaxDepthSlots; ++d)
         cnt->nShadow[d] = cnt->nNee[d] = cnt->nHit[d] = cnt->nHitB[d] = cnt->nMiss[d] = cnt->fetch[0][d] = cnt->fetch[1][d] = cnt->fetch[2][d] = cnt->nNeeCulled[d] = 0;
     cnt->scrubbed = 0;
+    cnt->dropped = 0;
     if (carry) cnt->nActive[0] = a, cnt->nHit[0] = h, cnt->nHitB[0] = hb, cnt->nMiss[0] = m;
 }
 

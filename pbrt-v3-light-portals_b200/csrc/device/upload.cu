@@ -92,7 +92,7 @@ int pbrtgpu_create(int cuda_device, pbrtgpu_ctx **out) {
         for (size_t i = 0; i < primes.size(); ++i) sums[i] = acc, acc += primes[i];
         if ((e = cudaMalloc((void **)&ctx->dPrimes, primes.size() * sizeof(int))) != cudaSuccess) return bail(e, "cudaMalloc(primes)");
         if ((e = cudaMalloc((void **)&ctx->dPrimeSums, primes.size() * sizeof(int))) != cudaSuccess) return bail(e, "cudaMalloc(primeSums)");
-        if ((e = cudaMalloc((void **)&ctx->dTotals, 6 * sizeof(unsigned long long))) != cudaSuccess) return bail(e, "cudaMalloc(totals)");
+        if ((e = cudaMalloc((void **)&ctx->dTotals, 8 * sizeof(unsigned long long))) != cudaSuccess) return bail(e, "cudaMalloc(totals)");
         cudaMemcpy(ctx->dPrimes, primes.data(), primes.size() * sizeof(int), cudaMemcpyHostToDevice);
         cudaMemcpy(ctx->dPrimeSums, sums.data(), primes.size() * sizeof(int), cudaMemcpyHostToDevice);
         std::vector<unsigned long long> magic = primeMagics(primes);

@@ -39,13 +39,32 @@ inline void fillWaveParams(const pbrtgpu_render_params *rp, WaveParams *w) {
     w->shardCount = rp->shard_count > 0 ? rp->shard_count : 1;
 }
 
+// What both drivers of the stage functions (render_host.inc on the GPU, tests/hostsim on the CPU) refuse.
+// The bounce count of a path is an 8-bit field of its flags word; the reference has no limit, its shipped
+// scenes go up to maxdepth 100 (scenes/blender/lamp/out/lamp.pbrt:9).
+constexpr int kMaxMaxDepth = 255;
+constexpr int kMaxIterationsPerBatch = 4096;  // open-ended batches stop here; what is left is counted in pbrtgpu_stats.truncated_paths
+inline const char *validateRenderParams(const pbrtgpu_render_params *rp) {
+    if (rp->spp <= 0) return "spp must be positive";
+    if (rp->max_depth < 0 || rp->max_depth > kMaxMaxDepth) return "maxdepth out of range (0 .. 255)";
+    if (rp->shard_count > 1 && (rp->shard_index < 0 || rp->shard_index >= rp->shard_count)) return "shard_index out of range";
+    const int *cb = rp->cropped_bounds;
+    if (cb[2] <= cb[0] || cb[3] <= cb[1]) return "empty film";
+    if (rp->integrator != PBRTGPU_INTEGRATOR_PATH && rp->integrator != PBRTGPU_INTEGRATOR_DIRECT) return "unknown integrator";
+    return nullptr;
+}
+
 struct BatchPlan {
     int tilesX, tilesY, shardTiles;  // shardTiles = tiles t with t % shardCount == shardIndex
     int sppBegin, sppEnd;
     int sppChunk;        // samples of a pixel per batch
     int tilesPerBatch;
     int maxSlots;
-    int depthIters;      // wavefront iterations per batch
+    int depthIters;      // wavefront iterations a batch is known to need (a path makes at most maxDepth + 1 scene intersections)
+    int roundIters;      // iterations per round: WaveCounters has one slot per iteration of a round; between rounds the counters are
+                         // folded and the live queue becomes iteration 0 of the next round (k_batch_stats, carry)
+    int openEnded;       // the iteration count is not known in advance (directlighting tree walk; vertices on material-less
+                         // primitives, which do not count as bounces): rounds continue until the path queue is empty
     int branchPerSlot;   // directlighting tree mode: pending-branch entries per path slot (0 otherwise)
     int neeMult;         // light samples per vertex: the shadow / next-event queues hold maxSlots * neeMult entries
 };
@@ -107,7 +126,8 @@ inline BatchPlan planBatches(const pbrtgpu_render_params *rp, long long targetSl
     // tree mode: a path walks up to 2^maxdepth - 1 vertices, one per wavefront iteration.  The iterations run in
     // rounds of this many; after each round the host looks whether any path is left (render_host.inc, anotherRound)
     if (branchPerSlot > 0) p.depthIters = 2 * rp->max_depth + 2 + (hasNullMaterial ? 8 : 0);
-    if (p.depthIters > kMaxDepthSlots - 1) p.depthIters = kMaxDepthSlots - 1;  // stage d touches the counters of depth d + 1
+    p.roundIters = p.depthIters < kMaxDepthSlots - 1 ? p.depthIters : kMaxDepthSlots - 1;  // stage d touches the counters of depth d + 1
+    p.openEnded = (branchPerSlot > 0 || hasNullMaterial) ? 1 : 0;
     return p;
 }
 

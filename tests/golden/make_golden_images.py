@@ -36,6 +36,8 @@ CASES = {
     "portal_room_direct": ("portal_room.pbrt", {"STRATEGY": "portal", 'Integrator "path" "integer maxdepth" [4]': 'Integrator "directlighting"'}),
     # directlighting over glass and uber with Kt: Li recurses into reflection AND transmission (directlighting.cpp:91-95)
     "direct_glass_all": ("direct_glass.pbrt", {}),
+    # material-less boundaries: more wavefront iterations than maxdepth + 1 (the batch runs rounds until its queue is empty)
+    "null_shells": ("null_shells.pbrt", {}),
     "direct_glass_one": ("direct_glass.pbrt", {'"integer maxdepth" [5] "string strategy" "all"': '"integer maxdepth" [7] "string strategy" "one"'}),
 }
 
@@ -49,9 +51,13 @@ def scene_text(case):
 
 
 def main():
+    """No arguments: every case.  With case names: only those, merged into the existing file."""
     pbrt = os.path.join(ROOT, "oracle", "_ref", "pbrt")
     out = {}
-    for case in CASES:
+    only = sys.argv[1:]
+    if only:
+        out = dict(np.load(os.path.join(ROOT, "tests", "golden", "images.npz")))
+    for case in (only or CASES):
         with tempfile.TemporaryDirectory() as d:
             sp = os.path.join(d, "s.pbrt")
             open(sp, "w").write(scene_text(case))

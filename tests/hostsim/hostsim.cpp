@@ -126,6 +126,7 @@ extern "C" int hostsim_render(void *p, const pbrtgpu_render_params *rp, float *f
     for (size_t i = 0; i < primes.size(); ++i) sums[i] = acc, acc += primes[i];
     std::vector<uint16_t> perms = radicalInversePermutations(primes);
 
+    if (validateRenderParams(rp)) return 1;  // the same refusals as pbrtgpu_render (wave_setup.h)
     WaveParams w;
     memset(&w, 0, sizeof(w));
     fillWaveParams(rp, &w);
@@ -139,7 +140,7 @@ extern "C" int hostsim_render(void *p, const pbrtgpu_render_params *rp, float *f
     w.directTree = tree ? 1 : 0;
     w.branchCapacity = tree ? rp->max_depth : 0;
     if (const char *e = getenv("PBRTGPU_TREE_ROUND_ITERS"))  // tests: short rounds, so that the carry between rounds is exercised
-        if (tree && atoi(e) > 0 && atoi(e) < pl.depthIters) pl.depthIters = atoi(e);
+        if (tree && atoi(e) > 0 && atoi(e) < pl.roundIters) pl.roundIters = atoi(e);
     w.nSampleArrays = sampleArrayCount(rp, s->n_lights);
     w.hal.arrayEndDim = kArrayStartDim + 2 * w.nSampleArrays;
     const int *cb = rp->cropped_bounds;
@@ -169,8 +170,10 @@ extern "C" int hostsim_render(void *p, const pbrtgpu_render_params *rp, float *f
             parallelFor(w.nSlots, threads, [&](int64_t a, int64_t b) { for (int64_t i = a; i < b; ++i) stageRaygen(w, (int)i); });
             int cur = 0;
             bool firstRound = true;
-            for (bool again = true; again;) {
-            for (int d = 0; d < pl.depthIters; ++d) {
+            int itersDone = 0;
+            for (bool again = true; again;) {  // rounds, as render_host.inc runs them
+            const int roundLen = pl.openEnded ? pl.roundIters : std::min(pl.roundIters, pl.depthIters - itersDone);
+            for (int d = 0; d < roundLen; ++d) {
                 int n = cnt.nActive[d];
                 parallelFor(n, threads, [&](int64_t a, int64_t b) {
                     for (int64_t i = a; i < b; ++i) {
@@ -213,8 +216,9 @@ extern "C" int hostsim_render(void *p, const pbrtgpu_render_params *rp, float *f
             // tree mode: paths that still hold pending branches go through another round (render_host.inc, anotherRound)
             if (firstRound) totals[0] += cnt.nActive[0];
             firstRound = false;
-            int left = cnt.nActive[pl.depthIters];
-            again = w.directTree && left > 0;
+            itersDone += roundLen;
+            int left = cnt.nActive[roundLen];
+            again = left > 0 && (pl.openEnded ? itersDone < kMaxIterationsPerBatch : itersDone < pl.depthIters);
             memset(&cnt, 0, sizeof(cnt));
             cnt.nActive[0] = again ? left : 0;
             }

@@ -4,8 +4,12 @@
 
 namespace pg {
 
+// Debug builds only: -DPG_HOST_TRACE (tests/hostsim with g++) or -DPG_DEVICE_TRACE (an A/B build of the CUDA library,
+// tools/build_variants.py) print every vertex; render ONE sample (pixel_bounds of one pixel, one sample number) with them.
 #if !defined(__CUDACC__) && defined(PG_HOST_TRACE)
 #define PG_TRACE(...) fprintf(stderr, __VA_ARGS__)
+#elif defined(__CUDA_ARCH__) && defined(PG_DEVICE_TRACE)
+#define PG_TRACE(...) printf(__VA_ARGS__)
 #else
 #define PG_TRACE(...)
 #endif
@@ -187,6 +191,7 @@ PG_HD void stageShadePhased(const WaveParams &w, int depth, int cur, int pos, bo
         }
     }
     if (stock) Li = lightSampleLi(w.sc, li, it, uL0, uL1, &wi, &lightPdf, &pL);
+    if (stock) PG_TRACE("  light d=%d slot=%d dim=%d li=%d uL=(%.9g %.9g) uS=(%.9g %.9g) wi=(%.9g %.9g %.9g) pdf=%.9g Li=(%.9g %.9g %.9g) pL=(%.9g %.9g %.9g)\n", depth, slot, smp.dim, li, uL0, uL1, uS0, uS1, wi.x, wi.y, wi.z, lightPdf, Li.r, Li.g, Li.b, pL.p.x, pL.p.y, pL.p.z);
     sync(3);
 
     // ---- phase 4: BSDF value and pdf for the light sample; the shadow ray (integrator.cpp:142-184)
@@ -202,6 +207,7 @@ PG_HD void stageShadePhased(const WaveParams &w, int depth, int cur, int pos, bo
             int sp = atomicIncInt(&w.cnt->nShadow[depth]);
             storeRay(w.shadowRays, sp, sr);
             w.shadowContrib[sp] = f4(c.r, c.g, c.b, bitsToFloat((unsigned)slot));
+            PG_TRACE("  shadow d=%d slot=%d f=(%.9g %.9g %.9g) spdf=%.9g c=(%.9g %.9g %.9g) o=(%.9g %.9g %.9g) d=(%.9g %.9g %.9g)\n", depth, slot, f.r, f.g, f.b, scatteringPdf, c.r, c.g, c.b, sr.o.x, sr.o.y, sr.o.z, sr.d.x, sr.d.y, sr.d.z);
         }
     }
     sync(4);
@@ -477,6 +483,7 @@ PG_HD void addRadiance(const WaveParams &w, int slot, float r, float g, float b)
 
 // ---- stage 4a: shadow rays.  Unoccluded -> the light sample counts.
 PG_HD void stageShadowResolve(const WaveParams &w, int pos, bool occluded) {
+    PG_TRACE("  shadow resolve slot=%d occluded=%d c=(%.9g %.9g %.9g)\n", (int)floatToBits(w.shadowContrib[pos].w), (int)occluded, w.shadowContrib[pos].x, w.shadowContrib[pos].y, w.shadowContrib[pos].z);
     if (occluded) return;
     F4 c = w.shadowContrib[pos];
     int slot = (int)floatToBits(c.w);

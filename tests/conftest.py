@@ -64,6 +64,23 @@ def hostsim_lib():
 
 
 @pytest.fixture(scope="session")
+def hostsim_perturbed_lib():
+    """tests/hostsim built with -DPG_PERTURB_LIBM: sinf / cosf / acosf / atan2f one ulp off in half of the calls."""
+    out = os.path.join(ROOT, "tests", "_build", "libhostsim_perturbed.so")
+    src = os.path.join(ROOT, "tests", "hostsim", "hostsim.cpp")
+    dev = os.path.join(ROOT, "pbrt-v3-light-portals_b200", "csrc")
+    deps = [src] + [os.path.join(dp, f) for dp, _, fs in os.walk(dev) for f in fs if f.endswith(".h")]
+    if not os.path.exists(out) or any(os.path.getmtime(d) > os.path.getmtime(out) for d in deps):
+        os.makedirs(os.path.dirname(out), exist_ok=True)
+        subprocess.check_call(["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-fPIC", "-shared", "-pthread", "-DPG_PERTURB_LIBM", src, "-o", out])
+    lib = C.CDLL(out)
+    lib.hostsim_create.restype = C.c_void_p
+    lib.hostsim_create.argtypes = [C.c_void_p]
+    lib.hostsim_destroy.argtypes = [C.c_void_p]
+    return lib
+
+
+@pytest.fixture(scope="session")
 def ref_harness():
     """oracle/_ref/ref_harness (the reference's own code); None when not built."""
     path = os.path.join(REF_DIR, "ref_harness")

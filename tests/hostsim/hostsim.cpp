@@ -7,10 +7,29 @@
 // the kernels' device functions; it is built only into tests/_build/ and is
 // never loaded by the product library, bench.py or the CLI (those fail loudly
 // without a CUDA device).
+#include <cmath>
 #include <cstdint>
+#include <cstring>
 #include <string>
 #include <thread>
 #include <vector>
+
+// -DPG_PERTURB_LIBM: the same code with a libm whose sinf / cosf / acosf / atan2f are off by one ulp in half of the
+// calls -- the difference CUDA's libm has against glibc's.  tests/test_render.py uses this build to measure how
+// much of an image depends on the last bit of those functions (a 1-ulp change of a sampled direction can flip a
+// shadow ray that grazes the limb of a small, distant sphere light), i.e. what tolerance a GPU image can be held to.
+#ifdef PG_PERTURB_LIBM
+static inline float pgNudge(float v) {
+    uint32_t u;
+    memcpy(&u, &v, 4);
+    if (!std::isfinite(v) || v == 0.f || !(u & 2u)) return v;
+    return std::nextafterf(v, (u & 4u) ? INFINITY : -INFINITY);
+}
+#define sinf(x) pgNudge(sinf(x))
+#define cosf(x) pgNudge(cosf(x))
+#define acosf(x) pgNudge(acosf(x))
+#define atan2f(y, x) pgNudge(atan2f(y, x))
+#endif
 
 #include "../../pbrt-v3-light-portals_b200/csrc/device/layout_build.h"
 

@@ -9,13 +9,18 @@ shared mutable member, so scenes whose light has more than one portal are render
 multi-threaded reference image differs from the single-threaded one only in the order tiles are merged
 (~1e-7 relative).
 
-Per-case tolerances are about 10 x the value observed on a B200 (gpurun_out/parity_stats.jsonl of round 2,
-copied to profiles/r02_parity_stats.jsonl), not a blanket figure:
-  * scenes without specular transmission: what remains is the order of float atomics into a pixel and the last
-    ulp of CUDA's sinf / cosf / acosf against glibc's -> rel RMSE ~1e-7 .. 1e-6;
-  * scenes with glass (Cornell: FresnelSpecular picks reflection or transmission by `u < F`, rough dispersive
-    glass samples a microfacet normal): a last-ulp difference moves a handful of samples across a discrete
-    decision, each of which changes one pixel by 1/spp of a sample's radiance.
+Per-case tolerances are 4 .. 10 x the value observed on a B200 (profiles/r02_parity_stats.jsonl), not a blanket
+figure.  The CUDA path differs from the reference in two things only: the order of float atomics into a pixel
+(~1e-7), and the last bit of CUDA's sinf / cosf / acosf / atan2f against glibc's.  The second one moves a few
+samples across DISCRETE decisions, each of which changes one pixel by 1/spp of a sample's radiance:
+  * lamp / sandbox under directlighting: no such decision is reachable -> rel RMSE 2e-8 .. 2e-7;
+  * glass (Cornell: FresnelSpecular picks reflection or transmission by `u < F`), microfacet lobe choice (plastic
+    clutter in C3 / C4): a handful of samples -> rel RMSE 2e-5 .. 2e-4;
+  * killeroo: 0.1 % of the SAMPLES, because its light is a radius-3 sphere seen from up to 900 units away and a
+    shadow ray towards a sample near the sphere's limb is cut off -- or not -- by the sphere's own ill-conditioned
+    quadratic (traced in tests/test_render.py::test_one_ulp_of_libm_moves_killeroo_samples, which reproduces the
+    effect on the CPU with a libm nudged by one ulp).  The flips go both ways: the image mean agrees to 1e-8,
+    and `mean_rel` is what the killeroo case is held to (a lobe biased by 0.05 % would move it by 1e-4).
 """
 import json
 import os
@@ -114,13 +119,13 @@ def test_c1_cornell_512_64spp(pkg, gpu, monkeypatch):
     text = _variant(open(src).read(), spp=64, res=(512, 512))
     ref = reference_image(text, REF_SCENES, CORES)
     ours, st = gpu_image(pkg, gpu, text, REF_SCENES)
-    check("c1_cornell_512_64spp", ours, ref, dict(rel_rmse=2e-3, bad_frac=2e-3, mean_rel=2e-5), dict(launches=st.kernel_launches))
+    check("c1_cornell_512_64spp", ours, ref, dict(rel_rmse=3e-4, bad_frac=1e-4, mean_rel=5e-6), dict(launches=st.kernel_launches))
     many, st2 = gpu_image(pkg, gpu, text, REF_SCENES, batch_slots=2 << 20, monkeypatch=monkeypatch)
     assert st2.kernel_launches > 3 * st.kernel_launches  # really several batches
     assert (st2.camera_rays, st2.closest_rays, st2.shadow_rays) == (st.camera_rays, st.closest_rays, st.shadow_rays)
-    check("c1_cornell_512_64spp_2M_batches", many, ref, dict(rel_rmse=2e-3, bad_frac=2e-3, mean_rel=2e-5), dict(launches=st2.kernel_launches))
+    check("c1_cornell_512_64spp_2M_batches", many, ref, dict(rel_rmse=3e-4, bad_frac=1e-4, mean_rel=5e-6), dict(launches=st2.kernel_launches))
     # the batching itself changes no path: only the order of float atomics into a pixel
-    check("c1_batches_vs_one_batch", many, ours, dict(rel_rmse=1e-6))
+    check("c1_batches_vs_one_batch", many, ours, dict(rel_rmse=4e-5))  # 25-pixel Gaussian footprint: 25 atomics per sample
 
 
 # ---------------------------------------------------------------- C2: killeroo 1920 x 1080, one bench step (16 spp)
@@ -133,11 +138,11 @@ def test_c2_killeroo_1080p_bench_step(pkg, gpu, monkeypatch):
     text = _variant(open(src).read(), spp=16, res=(1920, 1080))
     ref = reference_image(text, REF_SCENES, CORES)
     ours, st = gpu_image(pkg, gpu, text, REF_SCENES)
-    check("c2_killeroo_1080p_16spp", ours, ref, dict(rel_rmse=1e-4, bad_frac=1e-4, mean_rel=1e-6), dict(launches=st.kernel_launches))
+    check("c2_killeroo_1080p_16spp", ours, ref, dict(rel_rmse=5e-4, bad_frac=0.03, mean_rel=1e-6), dict(launches=st.kernel_launches))
     many, st2 = gpu_image(pkg, gpu, text, REF_SCENES, batch_slots=6 << 20, monkeypatch=monkeypatch)
     assert st2.kernel_launches > 3 * st.kernel_launches
-    check("c2_killeroo_1080p_16spp_6M_batches", many, ref, dict(rel_rmse=1e-4, bad_frac=1e-4, mean_rel=1e-6))
-    check("c2_batches_vs_one_batch", many, ours, dict(rel_rmse=1e-6))
+    check("c2_killeroo_1080p_16spp_6M_batches", many, ref, dict(rel_rmse=5e-4, bad_frac=0.03, mean_rel=1e-6))
+    check("c2_batches_vs_one_batch", many, ours, dict(rel_rmse=4e-6, bad_frac=0.0))  # the same paths: only the order of atomics
 
 
 # ---------------------------------------------------------------- the fork's shipped portal scenes, unmodified
@@ -161,11 +166,14 @@ def test_shipped_portal_scenes(pkg, gpu, name, integrator):
     ref = reference_image(text, os.path.dirname(src), 1)
     ours, st = gpu_image(pkg, gpu, text, os.path.dirname(src))
     case = name.split("/")[1].replace(".pbrt", "") + ("_path" if integrator else "_as_shipped")
-    check(case, ours, ref, dict(rel_rmse=2e-5, bad_frac=1e-4, mean_rel=2e-6), dict(launches=st.kernel_launches))
+    # observed: lamp_as_shipped 1.9e-7, sandbox_as_shipped 1.6e-8, sandbox_path 7.9e-8; lamp_path 4.4e-4 with 2 of 250 000
+    # pixels off (metal lampshade, maxdepth 100: two samples take another microfacet branch)
+    tol = dict(rel_rmse=4e-3, bad_frac=1e-4, mean_rel=5e-6) if case == "lamp_path" else dict(rel_rmse=2e-6, bad_frac=1e-5, mean_rel=1e-7)
+    check(case, ours, ref, tol, dict(launches=st.kernel_launches))
 
 
 # ---------------------------------------------------------------- C3: the skylight room as SURVEY 8(d) specifies it
-C3_TOL = dict(rel_rmse=2e-5, bad_frac=1e-4, mean_rel=2e-6)
+C3_TOL = dict(rel_rmse=6e-4, bad_frac=4e-4, mean_rel=2e-6)  # observed at 16 spp: 5e-5 .. 8e-5, 2e-5 .. 4e-5, <= 1.3e-7
 
 
 @pytest.mark.parametrize("strategy", ["light", "portal", "projection"])
@@ -221,5 +229,6 @@ def test_c4_shaped_scene_in_several_batches(pkg, gpu, monkeypatch, tmp_path):
     ours, st = gpu_image(pkg, gpu, text, d, batch_slots=1 << 20, monkeypatch=monkeypatch)
     one, st1 = gpu_image(pkg, gpu, text, d)
     assert st.kernel_launches >= 3 * st1.kernel_launches
-    check("c4_500k_tris_4_batches", ours, ref, dict(rel_rmse=2e-5, bad_frac=1e-4, mean_rel=2e-6))
-    check("c4_500k_tris_one_batch", one, ref, dict(rel_rmse=2e-5, bad_frac=1e-4, mean_rel=2e-6))
+    check("c4_500k_tris_4_batches", ours, ref, dict(rel_rmse=2e-3, bad_frac=6e-4, mean_rel=2e-6))  # observed 2.3e-4, 6e-5, 1e-7
+    check("c4_500k_tris_one_batch", one, ref, dict(rel_rmse=2e-3, bad_frac=6e-4, mean_rel=2e-6))
+    check("c4_batches_vs_one_batch", ours, one, dict(rel_rmse=4e-6, bad_frac=0.0))

@@ -219,6 +219,7 @@ def test_gpu_matches_reference_image(pkg, gpu, golden, case):
     sb = hs.params.sample_bounds
     assert stats.camera_rays == (sb[2] - sb[0]) * (sb[3] - sb[1]) * hs.params.spp
     assert stats.scrubbed == 0 and stats.kernel_launches > 0
+    assert stats.truncated_paths == 0 and stats.nee_rays_dropped == 0
 
 
 @pytest.mark.gpu
@@ -409,3 +410,29 @@ def test_gpu_analytic_scene_radiance(pkg, gpu, name):
     film, _ = gpu.render(hs.params)
     mean = float(hs.film_to_rgb(film).mean())
     assert abs(mean - 1.0) <= 0.02, mean
+
+
+# ---------------------------------------------------------------- how much of an image hangs on the last bit of libm
+def test_one_ulp_of_libm_moves_killeroo_samples(pkg, hostsim_lib, hostsim_perturbed_lib):
+    """What the GPU image tolerances rest on (tests/test_baseline_scenes.py).  The CUDA path differs from the
+    reference in nothing but the last bit of sinf / cosf / acosf / atan2f -- yet on killeroo-simple.pbrt 0.1 % of the
+    SAMPLES come out a few per cent different (unbiased: the image mean agrees to 1e-8).  Traced on a B200
+    (tools/gpu_diff_samples.py --trace): the light is a sphere of radius 3 seen from up to 900 units away; a light
+    sample near its limb gives a shadow ray that grazes the sphere, the sphere's quadratic (sphere.cpp:60-77) then
+    has a discriminant of the size of its own rounding error, and whether the ray is cut off just before its end
+    (tMax = 1 - ShadowEpsilon) flips when the shading point moves by 1e-4 -- which a 1-ulp change of the cosine-
+    hemisphere sample two bounces earlier does.  The reference itself has this knife edge: here the same device code
+    runs on the CPU twice, once with glibc's libm and once with those four functions nudged by one ulp in half of
+    the calls, and the two images differ as much as the GPU's does from the reference's."""
+    src = scene_path("killeroo-path.pbrt")
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    from dev_compare import variant
+    hs = pkg.HostScene(text=variant(open(src).read(), 2, (480, 270)), base_dir=os.path.dirname(src))
+    a, fa, _ = util.hostsim_render(hostsim_lib, hs)
+    b, fb, _ = util.hostsim_render(hostsim_perturbed_lib, hs)
+    s = util.image_stats(b, a)
+    d = np.abs(fa[..., :3].astype(np.float64) - fb[..., :3]).max(axis=2) / np.maximum(np.abs(fa[..., :3]).max(axis=2), 1e-6)
+    moved = float((d > 1e-3).mean())
+    # B200, same scene at 960 x 540: 0.11 % of the samples move by more than 1e-3 relative (gpurun_out/r02c_diff.log)
+    assert 1e-4 < moved < 1e-2, (moved, s)
+    assert s["mean_rel"] < 2e-4, s  # unbiased: flips go both ways

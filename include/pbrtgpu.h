@@ -210,6 +210,17 @@ int pbrtgpu_upload_scene(pbrtgpu_ctx *ctx, const pbrtgpu_scene *scene);
 int pbrtgpu_intersect_closest(pbrtgpu_ctx *ctx, const float *rays, int64_t n,
                               int32_t *prim_orig_id, float *t, float *b0b1);
 int pbrtgpu_intersect_any(pbrtgpu_ctx *ctx, const float *rays, int64_t n, uint8_t *occluded);
+/* pbrtgpu_intersect_closest for callers that must not allocate (CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc).  It has NO counterpart in the reference.
+ * Same arguments and results as pbrtgpu_intersect_closest, but the device-side staging of rays and hit
+ * records and the kernel's queue cursor live in one file-scope device array (csrc/device/noalloc.cu) that every GPU
+ * loading the library holds until exit: 2 MiB + 256 B.  No cudaMalloc / cudaFree, no host allocation on the success
+ * path.  n > PBRTGPU_NOALLOC_MAX_RAYS is refused with PBRTGPU_ERR_INVALID.  All calls on one GPU share the array (it
+ * keeps the last call's contents; the cursor is cleared by every call): calls that overlap on a GPU race -- the
+ * caller serialises them. */
+#define PBRTGPU_NOALLOC_MAX_RAYS 32768
+int pbrtgpu_intersect_closest_noalloc(pbrtgpu_ctx *ctx, const float *rays, int64_t n,
+                                      int32_t *prim_orig_id, float *t, float *b0b1);
 int pbrtgpu_intersect_closest_device(pbrtgpu_ctx *ctx, const void *d_rays, int64_t n,
                                      void *d_hits /* n*16 B {origId,t,b0,b1} */, float *elapsed_ms);
 int pbrtgpu_intersect_any_device(pbrtgpu_ctx *ctx, const void *d_rays, int64_t n,

@@ -20,6 +20,7 @@ _LIB = os.path.join(_PKG, "lib")
 
 MAT_STRIDE, LIGHT_STRIDE, PLANE_STRIDE, SPHERE_STRIDE, PORTAL_STRIDE = 24, 48, 48, 48, 16
 N_HALTON_PERMS = 3682913
+NOALLOC_MAX_RAYS = 32768  # PBRTGPU_NOALLOC_MAX_RAYS
 
 
 class PbrtGpuError(RuntimeError):
@@ -147,6 +148,8 @@ def gpu_lib():
         lib.pbrtgpu_intersect_closest_device.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, _p(C.c_float)]
         lib.pbrtgpu_intersect_any_device.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, _p(C.c_float)]
         lib.pbrtgpu_set_stream.argtypes = [C.c_void_p, C.c_void_p]
+        if hasattr(lib, "pbrtgpu_intersect_closest_noalloc"):
+            lib.pbrtgpu_intersect_closest_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]
         if hasattr(lib, "pbrtgpu_render"):
             lib.pbrtgpu_render.argtypes = [C.c_void_p, _p(RenderParams), C.c_void_p, _p(Stats)]
             lib.pbrtgpu_render_device.argtypes = [C.c_void_p, _p(RenderParams), _p(C.c_void_p), _p(Stats)]
@@ -251,6 +254,16 @@ class GpuContext:
         t = np.empty(n, np.float32)
         b = np.empty((n, 2), np.float32)
         self._check(self._lib.pbrtgpu_intersect_closest(self._h, rays.ctypes.data, n, ids.ctypes.data, t.ctypes.data, b.ctypes.data))
+        return ids, t, b
+
+    def intersect_closest_noalloc(self, rays):
+        """pbrtgpu_intersect_closest_noalloc: at most NOALLOC_MAX_RAYS rays, scratch in a fixed device array."""
+        rays = np.ascontiguousarray(rays, dtype=np.float32).reshape(-1, 8)
+        n = rays.shape[0]
+        ids = np.empty(n, np.int32)
+        t = np.empty(n, np.float32)
+        b = np.empty((n, 2), np.float32)
+        self._check(self._lib.pbrtgpu_intersect_closest_noalloc(self._h, rays.ctypes.data, n, ids.ctypes.data, t.ctypes.data, b.ctypes.data))
         return ids, t, b
 
     def intersect_any(self, rays):

@@ -165,6 +165,144 @@ def reference_arm(args):
         "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
 
+def ncu_kernel_figures(kernel_substr):
+    """Lanes per instruction, issue rate and L2 hit rate of a kernel from the newest committed ncu summary under
+    profiles/ (tools/ncu_summary.py over an `ncu --set full` capture of this same bench command): the average over
+    the captured launches of that kernel, weighted by their duration."""
+    import glob
+    best = None
+    for path in sorted(glob.glob(os.path.join(ROOT, "profiles", "*ncu*summary*.txt"))):
+        blocks, cur, rec = [], None, {}
+        for line in list(open(path)) + ["----"]:
+            if line.startswith("----"):
+                if cur and kernel_substr in cur and {"lanes", "issue", "ms"} <= set(rec):
+                    blocks.append(rec)
+                cur, rec = line, {}
+            elif "gpu__time_duration.sum" in line:
+                rec["ms"] = float(line.split()[-1])
+            elif "smsp__thread_inst_executed_per_inst_executed.ratio" in line:
+                rec["lanes"] = float(line.split()[-1])
+            elif "sm__inst_executed.sum.pct_of_peak_sustained_elapsed" in line:
+                rec["issue"] = float(line.split()[-1]) / 100.0
+            elif "lts__t_sector_hit_rate.pct" in line:
+                rec["l2_hit"] = float(line.split()[-1]) / 100.0
+        if blocks:
+            w = sum(r["ms"] for r in blocks)
+            best = {k: sum(r.get(k, 0.0) * r["ms"] for r in blocks) / w for k in ("lanes", "issue", "l2_hit")}
+            best.update(source=os.path.basename(path), launches=len(blocks))
+    return best
+
+
+def reference_image(text, base_dir, threads):
+    """One render of the reference binary (float PFM), for the rel_rmse of other_configs."""
+    pbrt = os.path.join(ROOT, "oracle", "_ref", "pbrt")
+    if not os.path.exists(pbrt):
+        return None
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    from dev_compare import read_pfm
+    tmp = os.path.join(base_dir, "_bench_oc_%d.pbrt" % os.getpid())
+    out = os.path.join(tempfile.gettempdir(), "_bench_oc_%d.pfm" % os.getpid())
+    open(tmp, "w").write(text)
+    try:
+        subprocess.check_call([pbrt, "--nthreads", str(threads), "--quiet", "--minloglevel", "2", "--outfile", out, tmp],
+                              stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+        return read_pfm(out)
+    finally:
+        os.unlink(tmp)
+        if os.path.exists(out):
+            os.unlink(out)
+
+
+def other_configs(pk, device):
+    """BASELINE.json's other configurations, after the timed region (N = 1): short device-timed runs at the named
+    size, each with a check against the reference -- images: rel RMSE against oracle/_ref/pbrt at 8 spp (the full-size
+    comparisons are tests/test_baseline_scenes.py); ray batches: IDs / t bits / occlusion flags of the first 2 M rays of
+    the timed batch against the reference's BVHAccel (tools/bench_rays.py checks whole 100 M batches)."""
+    import numpy as np
+    import torch
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import gen_c3
+    import util
+    cores = os.cpu_count() or 1
+    out = {}
+    ctx = pk.GpuContext(device)
+    ctx.set_stream(torch.cuda.current_stream().cuda_stream)
+
+    def image_config(name, text_of_spp, base_dir, spp):
+        hs = pk.HostScene(text=text_of_spp(spp), base_dir=base_dir)
+        ctx.upload(hs)
+        best = None
+        for _ in range(3):
+            _, st = ctx.render_device(hs.params)
+            best = st.device_ms if best is None else min(best, st.device_ms)
+        ctx.set_profile(True)
+        ctx.render_device(hs.params)
+        prof = ctx.get_profile()
+        ctx.set_profile(False)
+        tot = sum(v["ms"] for v in prof.values()) or 1.0
+        sbb = hs.params.sample_bounds
+        samples = (sbb[2] - sbb[0]) * (sbb[3] - sbb[1]) * hs.params.spp
+        rec = {"value": samples / best / 1e3, "unit": UNIT, "samples": samples, "device_ms": best,
+               "rays_per_sample": (st.closest_rays + st.shadow_rays) / samples, "share_of_step": {k: v["ms"] / tot for k, v in prof.items()}}
+        small = pk.HostScene(text=text_of_spp(8), base_dir=base_dir)
+        ref = reference_image(text_of_spp(8), base_dir, cores)
+        if ref is not None:
+            ctx.upload(small)
+            film, _ = ctx.render(small.params)
+            s = util.image_stats(small.film_to_rgb(film), ref)
+            rec["rel_rmse"], rec["mean_rel"], rec["checked"] = s["rel_rmse"], s["mean_rel"], "same scene at 8 spp against oracle/_ref/pbrt (%d threads)" % cores
+        out[name] = rec
+
+    ref_scenes = os.path.join(ROOT, "oracle", "_ref", "scenes")
+    c1 = os.path.join(ref_scenes, "cornell-path.pbrt")
+    if os.path.exists(c1):
+        image_config("C1 cornell_dielectric path maxdepth 5, 512x512, 64 spp", lambda spp: scene_variant(c1, spp, (512, 512)), ref_scenes, 64)
+    for strategy in ("light", "portal", "projection"):
+        image_config("C3 skylight room (tools/gen_c3.py), 512x512, 64 spp, strategy " + strategy,
+                     lambda spp, s=strategy: gen_c3.scene_text(s, spp, 512, "ceiling"), tempfile.gettempdir(), 64)
+    kil = os.path.join(ref_scenes, "killeroo-path.pbrt")
+    harness = os.path.join(ROOT, "oracle", "_ref", "ref_harness")
+    if os.path.exists(kil):
+        hs = pk.HostScene(kil)
+        ctx.upload(hs)
+        n, k = 10_000_000, 2_000_000
+        box = ([-100, -100, -150], [100, 150, 50])
+        sets = {"incoherent closest": (lambda: util.rays_incoherent_closest(hs.view, n, seed=42), False),
+                "toward-object closest": (lambda: util.rays_toward_box(n, box[0], box[1], seed=44), False),
+                "incoherent any-hit": (lambda: util.rays_shadow(hs.view, n, seed=43), True),
+                "object-bound any-hit": (lambda: util.rays_shadow(hs.view, n, seed=46, lo=np.array(box[0], float) * 1.5, hi=np.array(box[1], float) * 1.5), True)}
+        shm = "/dev/shm" if os.path.isdir("/dev/shm") else tempfile.gettempdir()
+        for name, (make, any_hit) in sets.items():
+            rays = make()
+            d_rays = torch.from_numpy(rays).cuda()
+            d_out = torch.empty(n * (1 if any_hit else 16), dtype=torch.uint8, device="cuda")
+            ms = min(ctx.intersect_device(d_rays.data_ptr(), n, d_out.data_ptr(), any_hit) for _ in range(4))
+            rec = {"value": n / ms / 1e3, "unit": "Mrays/s", "rays": n, "device_ms": ms}
+            if os.path.exists(harness):
+                rp, op = os.path.join(shm, "_oc_rays_%d.bin" % os.getpid()), os.path.join(shm, "_oc_out_%d.bin" % os.getpid())
+                rays[:k].tofile(rp)
+                try:
+                    subprocess.run([harness, "intersect", kil, rp, op, "any" if any_hit else "closest", str(cores)], stdout=subprocess.DEVNULL,
+                                   stderr=subprocess.DEVNULL, check=True)
+                    got = d_out.cpu().numpy()
+                    if any_hit:
+                        same = bool(np.array_equal(got[:k], np.fromfile(op, np.uint8)))
+                    else:
+                        want = np.fromfile(op, np.uint32).reshape(-1, 2)
+                        g = got.view(np.uint32).reshape(-1, 4)[:k]
+                        hit = want[:, 0] != 0xFFFFFFFF
+                        same = bool(np.array_equal(g[:, 0], want[:, 0]) and np.array_equal(g[hit, 1], want[hit, 1]))
+                    rec["bit_exact"], rec["rays_checked"] = same, k
+                finally:
+                    for f in (rp, op):
+                        if os.path.exists(f):
+                            os.unlink(f)
+            out["C5 killeroo BVH, 10 M rays, " + name] = rec
+            del d_rays, d_out
+    ctx.close()
+    return out
+
 
 def main():
     ap = argparse.ArgumentParser()
@@ -174,6 +312,7 @@ def main():
     ap.add_argument("--impl", default="ours")
     ap.add_argument("--spp-per-step", type=int, default=16)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-other-configs", action="store_true", help="skip the short runs of C1 / C3 / C5 after the timed region (N = 1 only)")
     ap.add_argument("--workload", default="killeroo", help="killeroo (BASELINE.json configs[1], the default) | c4[:quads] (configs[3])")
     args = ap.parse_args()
     global WORKLOAD, RES, TOTAL_SPP, METRIC
@@ -206,21 +345,37 @@ def main():
     params.shard_index, params.shard_count = rank, world
     cb = params.cropped_bounds
     n_pix = (cb[2] - cb[0]) * (cb[3] - cb[1])
-    film_t = torch.zeros(n_pix * 4, dtype=torch.float32, device="cuda")
+    # The film of step k is accumulated straight in film_t[k % 2] (pbrtgpu_render_device_into: no staging copy, no host
+    # synchronisation) and handed to NCCL as it is; the reduce is issued asynchronously, so it runs on NCCL's stream
+    # while the kernels of step k + 1 run on ours.  Two buffers: step k + 2 waits for the reduce of step k.
+    film_t = [torch.zeros(n_pix * 4, dtype=torch.float32, device="cuda") for _ in range(2)]
+    pending = [None, None]
     sb = params.sample_bounds
     samples_per_step = (sb[2] - sb[0]) * (sb[3] - sb[1]) * S * world  # whole job, all ranks
 
-    def step(k):
+    def set_range(k):
         params.spp_begin = (k * S * world) % TOTAL_SPP
         params.spp_end = params.spp_begin + S * world
-        _, st = ctx.render_device(params)
+
+    def step(k):
+        set_range(k)
+        b = k % 2
+        if pending[b] is not None:
+            pending[b].wait()  # orders our stream behind the reduce that last read this buffer (issued two steps ago)
+            pending[b] = None
+        ctx.render_device_into(params, film_t[b].data_ptr())
         if world > 1:
-            ctx.copy_film_device(film_t.data_ptr(), n_pix * 16)
-            dist.reduce(film_t, 0)
-        return st
+            pending[b] = dist.reduce(film_t[b], 0, async_op=True)
+
+    def drain():
+        for b in range(2):
+            if pending[b] is not None:
+                pending[b].wait()
+                pending[b] = None
 
     for k in range(args.warmup):
         step(k)
+    drain()
     torch.cuda.synchronize()
     clocks = ClockSampler(local) if rank == 0 else None
     if clocks:
@@ -232,18 +387,18 @@ def main():
         dist.barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     torch.cuda.synchronize()
+    launches0 = ctx.kernel_launches()
     e0.record(stream)
-    launches, rays = 0, 0
     for k in range(args.steps):
-        st = step(args.warmup + k)
-        launches += st.kernel_launches
-        rays += st.closest_rays + st.shadow_rays
+        step(args.warmup + k)
+    drain()  # the last reduces are inside the timed region
     e1.record(stream)
     torch.cuda.synchronize()
+    launches = ctx.kernel_launches() - launches0
     if world > 1:
         dist.barrier()
     ms = torch.tensor([e0.elapsed_time(e1)], device="cuda")
-    tot = torch.tensor([float(launches), float(rays)], device="cuda", dtype=torch.float64)
+    tot = torch.tensor([float(launches)], device="cuda", dtype=torch.float64)
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         dist.all_reduce(tot)
@@ -251,25 +406,61 @@ def main():
     clk = clocks.finish() if clocks else None
     value = samples_per_step * args.steps / (ms / 1e3) / 1e6
 
-    # ---- e2e: host buffers through the C ABI (scene H2D + render + film D2H), wall clock
+    # ---- N > 1: is the film NCCL reduced the image?  One more step; rank 0 then renders the SAME sample numbers alone
+    # (shard_count 1) and compares (the N-GPU image equals the 1-GPU image up to float summation order).
+    film_check = None
+    if world > 1:
+        set_range(0)
+        ctx.render_device_into(params, film_t[0].data_ptr())
+        dist.reduce(film_t[0], 0)
+        torch.cuda.synchronize()
+        if rank == 0:
+            solo = params.copy()
+            solo.shard_index, solo.shard_count = 0, 1
+            ctx.render_device_into(solo, film_t[1].data_ptr())
+            torch.cuda.synchronize()
+            a, b = film_t[0].double().view(-1, 4), film_t[1].double().view(-1, 4)
+            rel_rmse = float(torch.sqrt(((a[:, :3] - b[:, :3]) ** 2).mean()) / b[:, :3].abs().mean())
+            w_equal = bool(torch.equal(film_t[0].view(-1, 4)[:, 3], film_t[1].view(-1, 4)[:, 3]))
+            film_check = {"rel_rmse_vs_1gpu_render_of_same_samples": rel_rmse, "filter_weight_sums_equal": w_equal,
+                          "spp_compared": S * world, "tolerance": 1e-6, "ok": bool(rel_rmse <= 1e-6 and w_equal)}
+        dist.barrier()
+
+    # ---- e2e: the same step through the C ABI with HOST buffers, wall clock, per rank: H2D of the flattened scene
+    # (pbrtgpu_upload_scene), the kernels, at N > 1 the NCCL reduce of the film, D2H of the film into pinned memory
+    # (rank 0 at N > 1: the other ranks' films end in the reduce).  upload and render are also timed separately.
     view = hs.view
     scene_bytes = (view.n_nodes * (24 + 4 + 2 + 1) + view.n_prims * (1 + 1 + 4 * 4 + 36 + (36 if view.tri_n else 0) + (24 if view.tri_uv else 0)))
     e2e_steps = max(2, min(args.steps, 4))
-    film_host = torch.empty((cb[3] - cb[1], cb[2] - cb[0], 4), dtype=torch.float32, pin_memory=True).numpy()  # pinned result buffer
-    ctx.upload(hs)
-    ctx.render(params, out=film_host)
+    film_host_t = torch.empty((cb[3] - cb[1], cb[2] - cb[0], 4), dtype=torch.float32, pin_memory=True)
+    film_host = film_host_t.numpy()
+
+    def e2e_step(k):
+        set_range(k)
+        t0 = time.perf_counter()
+        ctx.upload(hs)
+        t1 = time.perf_counter()
+        if world == 1:
+            ctx.render(params, out=film_host)
+        else:
+            ctx.render_device_into(params, film_t[0].data_ptr())
+            dist.reduce(film_t[0], 0)
+            if rank == 0:
+                film_host_t.view(-1).copy_(film_t[0], non_blocking=True)
+            torch.cuda.synchronize()
+        t2 = time.perf_counter()
+        return (t1 - t0) * 1e3, (t2 - t1) * 1e3
+
+    e2e_step(0)
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
     t0 = time.perf_counter()
-    e2e_step_ms = []
+    e2e_upload_ms, e2e_render_ms = [], []
     for k in range(e2e_steps):
-        ts = time.perf_counter()
-        params.spp_begin = (k * S * world) % TOTAL_SPP
-        params.spp_end = params.spp_begin + S * world
-        ctx.upload(hs)
-        film, _ = ctx.render(params, out=film_host)
-        e2e_step_ms.append(round((time.perf_counter() - ts) * 1e3, 2))
+        u, r = e2e_step(k)
+        e2e_upload_ms.append(round(u, 2))
+        e2e_render_ms.append(round(r, 2))
     t_e2e = torch.tensor([time.perf_counter() - t0], device="cuda", dtype=torch.float64)
     if world > 1:
         dist.all_reduce(t_e2e, op=dist.ReduceOp.MAX)
@@ -305,11 +496,25 @@ def main():
     achieved = alg_bytes / (tc["ms"] / 1e3) / 1e9 if tc["ms"] > 0 else 0.0
     traffic, traffic_src = None, None
     import glob
-    for tp in sorted(glob.glob(os.path.join(ROOT, "profiles", "*traffic.json"))) if WORKLOAD == "killeroo" else []:
+    tag = "c4" if WORKLOAD.startswith("c4") else "killeroo"
+    for tp in sorted(glob.glob(os.path.join(ROOT, "profiles", "*traffic*.json"))):
         tj = json.load(open(tp))
-        traffic, traffic_src = tj["dram_bytes_read"] + tj["dram_bytes_write"], os.path.basename(tp) + ": " + tj["capture"]
-    roofline = {"kernel": "k_ptrace_fused (+ k_ptrace_closest for the camera rays)", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": traffic, "traffic_source": traffic_src, "alg_bytes_per_launch": alg_bytes / max(1, tc["launches"]), "peak_source": peak_src, "launches": tc["launches"], "avg_launch_ms": tc["ms"] / max(1, tc["launches"]),
+        if tj.get("workload", "killeroo") == tag:
+            traffic, traffic_src = tj["dram_bytes_read"] + tj["dram_bytes_write"], os.path.basename(tp) + ": " + tj["capture"]
+    alg_per_launch = alg_bytes / max(1, tc["launches"])
+    ncu = ncu_kernel_figures("k_ptrace_fused") if tag == "killeroo" else None
+    # What bounds the kernel: on killeroo the BVH (9 MB) is served by L1 / L2 and DRAM sees 5 % of the algorithmic bytes --
+    # the limiter is the SM's issue rate times the share of lanes that do work.  `achieved / peak / frac` stay the
+    # HBM-normalised figures of SURVEY.md 8(d), the common yardstick; they are not a claim that the kernel is at 63 %
+    # of a memory roofline.
+    roofline = {"kernel": "k_ptrace_fused (+ k_ptrace_closest for the camera rays)",
+                "bound": "issue" if tag == "killeroo" else "hbm", "yardstick": "hbm (SURVEY.md 8(d) algorithmic bytes / measured copy bandwidth)",
+                "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "issue_frac": ncu["issue"] if ncu else None, "lanes_per_inst": ncu["lanes"] if ncu else None,
+                "thread_inst_frac": (ncu["issue"] * ncu["lanes"] / 32.0) if ncu else None, "l2_hit": ncu.get("l2_hit") if ncu else None,
+                "ncu_source": ncu["source"] if ncu else None,
+                "traffic": traffic, "traffic_ratio": (traffic / alg_per_launch) if traffic else None, "traffic_source": traffic_src,
+                "alg_bytes_per_launch": alg_per_launch, "peak_source": peak_src, "launches": tc["launches"], "avg_launch_ms": tc["ms"] / max(1, tc["launches"]),
                 "node_tests_per_ray": node_tests / max(1, all_rays), "prim_tests_per_ray": prim_tests / max(1, all_rays),
                 "rays_in_profile_step": {"path_closest": int(path_rays), "nee_closest": int(pst.nee_closest_rays), "shadow_any": int(pst.shadow_rays),
                                          "camera": int(pst.camera_rays)},
@@ -320,12 +525,17 @@ def main():
            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
            "data": "reference scene file" if "reference scene" in scene_desc else "synthetic",
            "config": {"workload": scene_desc + ", %dx%d" % RES + ", Integrator path maxdepth 5, halton; one step = %d spp of the full frame per GPU "
-                      "(sample numbers of the %d-spp job), 16x16 tiles sharded over ranks, film reduce per step" % (S, TOTAL_SPP),
+                      "(sample numbers of the %d-spp job), 16x16 tiles sharded over ranks, film reduce per step (asynchronous: it overlaps the next step)" % (S, TOTAL_SPP),
                       "spp_per_step_per_gpu": S, "l2": "wavefront state of a step (%.0f MB) and the film exceed L2; no flush needed" %
-                      (min(samples_per_step // world, 64 << 20) * 290 / 1e6), "rays_per_sample": float(tot[1].item()) / (samples_per_step * args.steps)},
+                      (min(samples_per_step // world, 64 << 20) * 290 / 1e6),
+                      "rays_per_sample": float(all_rays) / (samples_per_step / world) if world == 1 else float(all_rays) * world / samples_per_step},
            "gpu_launches": int(tot[0].item()), "clocks": clk,
-           "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(scene_bytes), "d2h_bytes_per_step": int(n_pix * 16), "steps": e2e_steps, "step_ms": e2e_step_ms},
+           "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(scene_bytes), "d2h_bytes_per_step": int(n_pix * 16), "steps": e2e_steps,
+                   "upload_ms": e2e_upload_ms, "render_ms": e2e_render_ms,
+                   "includes": "scene H2D + kernels + film D2H" + (" + NCCL reduce of the film; times are rank 0's, the value is the max over ranks" if world > 1 else "")},
            "roofline": roofline}
+    if film_check is not None:
+        out["film_check"] = film_check
     if not args.no_cpu_baseline and world == 1:
         cores = os.cpu_count() or 1
         r = run_reference_cpu(scene_path, 8, (RES[0] // 2, RES[1] // 2), cores)
@@ -333,6 +543,12 @@ def main():
             out["cpu_baseline"] = {"value": r["samples"] / r["render_s"] / 1e6, "unit": UNIT, "cores": cores, "kind": "reference",
                                    "sample": "960x540 at 8 spp, oracle/_ref/pbrt --nthreads %d, render time %.2f s (whole run %.2f s minus setup %.2f s)"
                                    % (cores, r["render_s"], r["whole_s"], r["setup_s"])}
+    if world == 1 and not args.no_other_configs and WORKLOAD == "killeroo":
+        ctx.close()
+        try:
+            out["other_configs"] = other_configs(pk, local)
+        except Exception as e:  # the headline line must not be lost to a side run
+            out["other_configs"] = {"error": repr(e)}
     print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()

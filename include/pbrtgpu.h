@@ -235,6 +235,16 @@ int pbrtgpu_render(pbrtgpu_ctx *ctx, const pbrtgpu_render_params *params,
 /* Same, film left on the device (for the NCCL reduce); *d_film is owned by ctx. */
 int pbrtgpu_render_device(pbrtgpu_ctx *ctx, const pbrtgpu_render_params *params,
                           void **d_film, pbrtgpu_stats *stats_or_null);
+/* Same, accumulated straight in a caller-owned device buffer (cropped W*H*4 floats, 16-byte aligned; e.g. the tensor
+ * handed to NCCL -- Film::MergeFilmTile film.cpp:117-130 across GPUs): no staging copy.  With stats_or_null == NULL the
+ * call does not wait for the GPU: it returns once the render is enqueued on the ctx's stream, so the caller can order an
+ * ncclReduce of this film behind it and start the next render while the reduce runs (renders whose iteration count is
+ * not known in advance -- material-less primitives, directlighting over specular transmission -- still synchronise
+ * between rounds).  The buffer must stay valid until that work has run. */
+int pbrtgpu_render_device_into(pbrtgpu_ctx *ctx, const pbrtgpu_render_params *params, void *d_film,
+                               pbrtgpu_stats *stats_or_null);
+/* Kernels launched by this context so far (host-side count, no device read-back). */
+int64_t pbrtgpu_kernel_launches(const pbrtgpu_ctx *ctx);
 /* Copy the film left by pbrtgpu_render_device into a caller-owned device buffer (e.g. a tensor handed to NCCL). */
 int pbrtgpu_copy_film_device(pbrtgpu_ctx *ctx, void *d_dst, int64_t bytes);
 /* Profile mode: renders record a CUDA-event pair around every kernel launch and count

@@ -153,6 +153,10 @@ def gpu_lib():
         if hasattr(lib, "pbrtgpu_render"):
             lib.pbrtgpu_render.argtypes = [C.c_void_p, _p(RenderParams), C.c_void_p, _p(Stats)]
             lib.pbrtgpu_render_device.argtypes = [C.c_void_p, _p(RenderParams), _p(C.c_void_p), _p(Stats)]
+        if hasattr(lib, "pbrtgpu_render_device_into"):
+            lib.pbrtgpu_render_device_into.argtypes = [C.c_void_p, _p(RenderParams), C.c_void_p, _p(Stats)]
+            lib.pbrtgpu_kernel_launches.argtypes = [C.c_void_p]
+            lib.pbrtgpu_kernel_launches.restype = C.c_int64
         if hasattr(lib, "pbrtgpu_set_profile"):
             lib.pbrtgpu_set_profile.argtypes = [C.c_void_p, C.c_int]
             lib.pbrtgpu_get_profile.argtypes = [C.c_void_p, _p(Profile)]
@@ -306,6 +310,15 @@ class GpuContext:
 
     def copy_film_device(self, dst_ptr, nbytes):
         self._check(self._lib.pbrtgpu_copy_film_device(self._h, C.c_void_p(dst_ptr), int(nbytes)))
+
+    def render_device_into(self, params, d_film_ptr, want_stats=False):
+        """Render into a caller-owned device film.  Without stats the call only enqueues (no host synchronisation)."""
+        stats = Stats() if want_stats else None
+        self._check(self._lib.pbrtgpu_render_device_into(self._h, C.byref(params), C.c_void_p(d_film_ptr), C.byref(stats) if want_stats else None))
+        return stats
+
+    def kernel_launches(self):
+        return int(self._lib.pbrtgpu_kernel_launches(self._h))
 
     def render_device(self, params):
         d_film = C.c_void_p()

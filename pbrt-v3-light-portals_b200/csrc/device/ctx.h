@@ -59,6 +59,8 @@ struct pbrtgpu_ctx {
     // render scratch, grown on demand
     pg::DeviceBuffer scratch[16];
     pg::DeviceBuffer film;
+    void *filmTarget = nullptr;  // pbrtgpu_render_device_into: the caller's device film for the render in progress (else `film`)
+    bool asyncRender = false;    // ... and, without a stats request, no host synchronisation at the end of the render
     int smCount = 148;
     // trace kernel variant (tuning knobs, env PBRTGPU_TRACE_PERSISTENT / _FETCH_THRESHOLD / _PERSIST_BLOCKS)
     bool tracePersistent = true;

@@ -295,6 +295,32 @@ def test_gpu_scheduling_knobs_do_not_change_the_image(pkg, gpu, monkeypatch, kno
 
 
 @pytest.mark.gpu
+def test_gpu_render_into_caller_film(pkg, gpu):
+    """pbrtgpu_render_device_into: the film accumulated straight in a caller-owned device buffer (the tensor bench.py
+    hands to NCCL) is the film pbrtgpu_render returns -- also when the buffer held another image before, and also
+    without a stats request (the call then only enqueues)."""
+    import torch
+    hs = load_case(pkg, "box_glass")
+    gpu.upload(hs)
+    want, _ = gpu.render(hs.params)
+    cb = hs.params.cropped_bounds
+    buf = torch.full(((cb[3] - cb[1]) * (cb[2] - cb[0]) * 4,), 7.0, dtype=torch.float32, device="cuda")
+    torch.cuda.synchronize()
+    st = gpu.render_device_into(hs.params, buf.data_ptr(), want_stats=True)
+    assert st.camera_rays > 0 and st.truncated_paths == 0
+    got = buf.cpu().numpy().reshape(want.shape)
+    assert util.image_stats(hs.film_to_rgb(got), hs.film_to_rgb(want))["rel_rmse"] <= 1e-5
+    n0 = gpu.kernel_launches()
+    assert gpu.render_device_into(hs.params, buf.data_ptr()) is None  # asynchronous form
+    assert gpu.kernel_launches() - n0 == st.kernel_launches
+    torch.cuda.synchronize()  # device-wide: the context renders on its own stream
+    got = buf.cpu().numpy().reshape(want.shape)
+    assert util.image_stats(hs.film_to_rgb(got), hs.film_to_rgb(want))["rel_rmse"] <= 1e-5
+    with pytest.raises(pkg.PbrtGpuError):
+        gpu.render_device_into(hs.params, buf.data_ptr() + 4)  # not 16-byte aligned
+
+
+@pytest.mark.gpu
 def test_gpu_render_errors(pkg, gpu):
     hs = load_case(pkg, "tri_soup")
     gpu.upload(hs)

@@ -246,6 +246,53 @@ PG_NI_BSDF Spec bsdfSampleF(const BSDF &b, V3 woW, V3 *wiW, float u0, float u1, 
     return f;
 }
 
+// ---- a BSDF that is ONE LambertianReflection (MatLobes::shadeClass 0): bsdfF / bsdfPdf / bsdfSampleF above with the lobe
+// loops, the lobe switch and the calls folded away.  Every arithmetic operation the general routines perform on such
+// a BSDF is performed here, in the same order, so the results are bit-identical (the shade kernel's Lambert
+// instantiation and its general one give the same image; tests/test_render.py knob PBRTGPU_SHADE_LAMBERT).
+//   BSDF::f        reflection.cpp:713-726   one matching lobe: f = reflect ? R / pi : 0
+//   BSDF::Pdf      reflection.cpp:814-829   pdf = SameHemisphere ? |cos| / pi : 0, divided by one matching component
+//   BSDF::Sample_f reflection.cpp:747-812   comp = 0, uRemapped = min(u0, 1 - eps), cosine-sampled wi, f re-evaluated
+PG_HD Spec lambertF(const BSDF &b, Spec R, V3 woW, V3 wiW) {
+    V3 wo = bsdfWorldToLocal(b, woW);
+    if (wo.z == 0) return spec(0.f);
+    bool reflect = dot(wiW, b.ng) * dot(woW, b.ng) > 0;
+    Spec f = spec(0.f);
+    if (reflect) f += R * kInvPi;
+    return f;
+}
+PG_HD float lambertPdf(const BSDF &b, V3 woW, V3 wiW) {
+    V3 wo = bsdfWorldToLocal(b, woW), wi = bsdfWorldToLocal(b, wiW);
+    if (wo.z == 0) return 0.f;
+    float pdf = 0.f;
+    pdf += sameHemisphere(wo, wi) ? absCosTheta(wi) * kInvPi : 0;
+    return pdf / 1;
+}
+PG_HD Spec lambertSampleF(const BSDF &b, Spec R, V3 woW, V3 *wiW, float u0, float u1, float *pdf, int *sampledType) {
+    int comp = (int)floorf(u0 * 1);
+    if (comp > 0) comp = 0;
+    float uR = minf(u0 * 1 - comp, kOneMinusEpsilon);
+    V3 wo = bsdfWorldToLocal(b, woW);
+    if (wo.z == 0) {
+        *pdf = 0;
+        *sampledType = 0;
+        return spec(0.f);
+    }
+    V3 wi = cosineSampleHemisphere(uR, u1);
+    if (wo.z < 0) wi.z *= -1;
+    *pdf = sameHemisphere(wo, wi) ? absCosTheta(wi) * kInvPi : 0;
+    *sampledType = BSDF_REFLECTION | BSDF_DIFFUSE;
+    if (*pdf == 0) {
+        *sampledType = 0;
+        return spec(0.f);
+    }
+    *wiW = bsdfLocalToWorld(b, wi);
+    bool reflect = dot(*wiW, b.ng) * dot(woW, b.ng) > 0;
+    Spec f = spec(0.f);
+    if (reflect) f += R * kInvPi;
+    return f;
+}
+
 // Material::ComputeScatteringFunctions for the material table of pbrtgpu.h
 // (allowMultipleLobes = true, TransportMode::Radiance, as path.cpp:107 calls it).
 //

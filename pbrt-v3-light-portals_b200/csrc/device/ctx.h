@@ -69,6 +69,9 @@ struct pbrtgpu_ctx {
     int lightStageBlocksPerSM = 16;  // grid of k_split_hits / k_post_trace, in 128-thread blocks per SM
     bool extPortalStrategy = false;  // a portal light of the uploaded scene uses a strategy the reference does not have
     bool sortHits = true;       // hit queue split by material class (render.cu:splitHits)
+    bool shadeLambert = true;   // the front run of the split queue is shaded by the Lambert instantiation of the shade kernel
+    int lambertBlock = 5122;    // its block shape: 5122 = 512 threads x 2 per SM, 5121, 3842, 2563, 2562 (A/B knob)
+    bool hasPortalLight = false;
     bool shadeSmemSet = false;  // k_shade_sync's shared-memory opt-in done on this device
     int shadeBlock = 5122;      // 512-thread blocks, two per SM (A/B in profiles/r01g_ab_shade.log)
     int fetchThreshold = 12;

@@ -103,7 +103,11 @@ struct ShadeScratch {
 };
 static_assert(sizeof(ShadeScratch) == 37 * 4, "ShadeScratch must stay an odd number of words");
 
-template <class Sync, bool EXT = true>
+// LAMBERT: every vertex handed in lies on a material whose BSDF is one LambertianReflection (MatLobes::shadeClass 0,
+// the front run of the hit queue) or on a primitive without a material; the BSDF calls are the closed forms of
+// bsdf_eval.h (same arithmetic, bit-identical results), and nothing of the lobe machinery is compiled in.
+// PORTAL = false: the scene has no portal light; the portal estimators are not compiled in.
+template <class Sync, bool EXT = true, bool LAMBERT = false, bool PORTAL = true>
 PG_HD void stageShadePhased(const WaveParams &w, int depth, int cur, int pos, bool active, Sync sync, ShadeScratch &scr) {
     const int flagsNS = BSDF_ALL & ~BSDF_SPECULAR;
     // ---- phase 0: path state, the hit record -> SurfaceInteraction, emitted light (path.cpp:91-96)
@@ -143,15 +147,20 @@ PG_HD void stageShadePhased(const WaveParams &w, int depth, int cur, int pos, bo
     smp.index = 0, smp.dim = 0;
     BSDF &bsdf = scr.bsdf;
     bsdf.nLobes = 0;
+    Spec lambertR = spec(0.f);
     if (scatter) {
         smp.index = w.hIndex[slot];
         smp.dim = w.dim[slot];
         makeBSDF(it, w.sc.matLobes, mat, w.sc.matParams + PBRTGPU_MAT_STRIDE * (size_t)mat, wvl0, &bsdf);
+        if (LAMBERT) {
+            const float *r = &w.sc.matLobes[mat].lobes[0].R.r;
+            lambertR = spec(PG_LD(r), PG_LD(r + 1), PG_LD(r + 2));
+        }
     }
     sync(1);
 
     // ---- phase 2: UniformSampleOneLight's samples and light pick (integrator.cpp:100-122)
-    bool nee = scatter && bsdfNumComponents(bsdf, flagsNS) > 0 && w.sc.nLights > 0;
+    bool nee = scatter && (LAMBERT || bsdfNumComponents(bsdf, flagsNS) > 0) && w.sc.nLights > 0;
     int li = 0, lightTag = 0;
     float pickPdf = 0, uL0 = 0, uL1 = 0, uS0 = 0, uS1 = 0;
     if (nee) {
@@ -168,7 +177,7 @@ PG_HD void stageShadePhased(const WaveParams &w, int depth, int cur, int pos, bo
     sync(2);
 
     // ---- phase 3: sample the light (EstimateDirect, integrator.cpp:133-141); portal lights take their own estimator
-    const bool portal = nee && lightTag == PBRTGPU_LIGHT_PORTAL_AREA;
+    const bool portal = PORTAL && nee && lightTag == PBRTGPU_LIGHT_PORTAL_AREA;
     const bool stock = nee && !portal;
     const bool isDelta = lightTag == PBRTGPU_LIGHT_POINT || lightTag == PBRTGPU_LIGHT_DISTANT || lightTag == PBRTGPU_LIGHT_SPOT;
     V3 wi = v3(0, 0, 0);  // Vector3f() is zero-initialised
@@ -196,8 +205,8 @@ PG_HD void stageShadePhased(const WaveParams &w, int depth, int cur, int pos, bo
 
     // ---- phase 4: BSDF value and pdf for the light sample; the shadow ray (integrator.cpp:142-184)
     if (stock && lightPdf > 0 && !isBlack(Li)) {
-        Spec f = bsdfF(bsdf, it.wo, wi, flagsNS) * absDot(wi, it.ns);
-        scatteringPdf = bsdfPdf(bsdf, it.wo, wi, flagsNS);
+        Spec f = (LAMBERT ? lambertF(bsdf, lambertR, it.wo, wi) : bsdfF(bsdf, it.wo, wi, flagsNS)) * absDot(wi, it.ns);
+        scatteringPdf = LAMBERT ? lambertPdf(bsdf, it.wo, wi) : bsdfPdf(bsdf, it.wo, wi, flagsNS);
         if (!isBlack(f)) {
             Spec Ld;
             if (isDelta) Ld = f * Li / lightPdf;
@@ -218,7 +227,8 @@ PG_HD void stageShadePhased(const WaveParams &w, int depth, int cur, int pos, bo
     bool sampledSpecular = false;
     if (misRay) {
         int sampledType;
-        fMis = bsdfSampleF(bsdf, it.wo, &wi, uS0, uS1, &scatteringPdf, flagsNS, &sampledType);
+        fMis = LAMBERT ? lambertSampleF(bsdf, lambertR, it.wo, &wi, uS0, uS1, &scatteringPdf, &sampledType)
+                       : bsdfSampleF(bsdf, it.wo, &wi, uS0, uS1, &scatteringPdf, flagsNS, &sampledType);
         fMis *= absDot(wi, it.ns);
         sampledSpecular = (sampledType & BSDF_SPECULAR) != 0;
         misRay = !isBlack(fMis) && scatteringPdf > 0;
@@ -263,7 +273,7 @@ PG_HD void stageShadePhased(const WaveParams &w, int depth, int cur, int pos, bo
         wi = v3(0, 0, 0);
         float u0, u1;
         get2D(w.hal, smp, &u0, &u1);
-        f = bsdfSampleF(bsdf, wo, &wi, u0, u1, &pdf, BSDF_ALL, &sampled);
+        f = LAMBERT ? lambertSampleF(bsdf, lambertR, wo, &wi, u0, u1, &pdf, &sampled) : bsdfSampleF(bsdf, wo, &wi, u0, u1, &pdf, BSDF_ALL, &sampled);
     }
     sync(7);
 
@@ -301,6 +311,11 @@ PG_HD void stageShadePhased(const WaveParams &w, int depth, int cur, int pos, bo
 PG_HD void stageShade(const WaveParams &w, int depth, int cur, int pos) {
     ShadeScratch scr;
     stageShadePhased(w, depth, cur, pos, true, NoSync(), scr);
+}
+// the Lambert instantiation, for callers that know the vertex's material class (tests/hostsim with PBRTGPU_HOSTSIM_LAMBERT)
+PG_HD void stageShadeLambert(const WaveParams &w, int depth, int cur, int pos) {
+    ShadeScratch scr;
+    stageShadePhased<NoSync, true, true, true>(w, depth, cur, pos, true, NoSync(), scr);
 }
 
 // ---- stage 3 for Integrator "directlighting": DirectLightingIntegrator::Li (directlighting.cpp:63-98)

@@ -222,10 +222,14 @@ struct BlockSync {
         if ((PG_SYNC_MASK >> i) & 1) __syncthreads();
     }
 };
-template <int BLOCK, int PER_SM, bool EXT = false>  // EXT: with the non-reference portal strategies (direct.h)
-__global__ void __launch_bounds__(BLOCK, PER_SM) k_shade_sync(const WaveParams *__restrict__ wp, int depth, int cur) {
+// EXT: with the non-reference portal strategies (direct.h).  LAMBERT / PORTAL: see stageShadePhased.
+// run: which part of the hit queue -- 0 = all of it, 1 = the front run (hits on single-Lambert-lobe materials and on
+// material-less primitives, render.cu:splitHits), 2 = the back run (every other material).
+template <int BLOCK, int PER_SM, bool EXT = false, bool LAMBERT = false, bool PORTAL = true>
+__global__ void __launch_bounds__(BLOCK, PER_SM) k_shade_sync(const WaveParams *__restrict__ wp, int depth, int cur, int run) {
     const WaveParams &w = *wp;
-    int n = hitQueueLen(w, depth);
+    const int nA = w.cnt->nHit[depth], nB = w.cnt->nHitB[depth];
+    const int begin = run == 2 ? nA : 0, end = run == 1 ? nA : nA + nB;
     int stride = gridDim.x * blockDim.x;
 #ifdef PG_SHADE_LOCAL_SCRATCH
     ShadeScratch scr;
@@ -233,10 +237,10 @@ __global__ void __launch_bounds__(BLOCK, PER_SM) k_shade_sync(const WaveParams *
     extern __shared__ __align__(16) unsigned char pgShadeSmem[];  // BLOCK * sizeof(ShadeScratch), see shadeSmemBytes
     ShadeScratch &scr = reinterpret_cast<ShadeScratch *>(pgShadeSmem)[threadIdx.x];
 #endif
-    for (int base = blockIdx.x * blockDim.x; base < n; base += stride) {
+    for (int base = begin + blockIdx.x * blockDim.x; base < end; base += stride) {
         int i = base + threadIdx.x;
-        bool active = i < n;
-        stageShadePhased<BlockSync, EXT>(w, depth, cur, active ? hitQueueAt(w, depth, i) : 0, active, BlockSync(), scr);
+        bool active = i < end;
+        stageShadePhased<BlockSync, EXT, LAMBERT, PORTAL>(w, depth, cur, active ? hitQueueAt(w, depth, i) : 0, active, BlockSync(), scr);
     }
 }
 

@@ -76,6 +76,8 @@ int pbrtgpu_create(int cuda_device, pbrtgpu_ctx **out) {
     if (const char *v = getenv("PBRTGPU_SHADE_SYNC")) ctx->shadeSync = atoi(v) != 0;
     if (const char *v = getenv("PBRTGPU_LIGHT_STAGE_BLOCKS")) ctx->lightStageBlocksPerSM = std::min(32, std::max(1, atoi(v)));
     if (const char *v = getenv("PBRTGPU_SORT_HITS")) ctx->sortHits = atoi(v) != 0;
+    if (const char *v = getenv("PBRTGPU_SHADE_LAMBERT")) ctx->shadeLambert = atoi(v) != 0;
+    if (const char *v = getenv("PBRTGPU_LAMBERT_BLOCK")) ctx->lambertBlock = atoi(v);
     if (const char *v = getenv("PBRTGPU_FETCH_THRESHOLD")) ctx->fetchThreshold = std::min(32, std::max(1, atoi(v)));
     if (const char *v = getenv("PBRTGPU_SHADE_BLOCK")) ctx->shadeBlock = atoi(v);
     if (const char *v = getenv("PBRTGPU_PHASE_BIAS")) ctx->phaseBias = std::min(1024, std::max(0, atoi(v)));
@@ -186,6 +188,9 @@ int pbrtgpu_upload_scene(pbrtgpu_ctx *ctx, const pbrtgpu_scene *s) {
     UP(s->light_prim, s->n_lights, &d.lightPrim);
     UP(s->light_strategy, s->n_lights, &d.lightStrategy);
     ctx->extPortalStrategy = false;
+    ctx->hasPortalLight = false;
+    for (int i = 0; i < s->n_lights; ++i)
+        if (s->light_tag[i] == PBRTGPU_LIGHT_PORTAL_AREA) ctx->hasPortalLight = true;
     for (int i = 0; i < s->n_lights; ++i)
         if (s->light_tag[i] == PBRTGPU_LIGHT_PORTAL_AREA && s->light_strategy && s->light_strategy[i] >= PBRTGPU_PORTAL_SOLIDANGLE) ctx->extPortalStrategy = true;
     {

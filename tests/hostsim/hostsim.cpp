@@ -176,6 +176,7 @@ extern "C" int hostsim_render(void *p, const pbrtgpu_render_params *rp, float *f
     bindWaveBuffers(&w, bufs);
     WaveCounters cnt;
     w.cnt = &cnt;
+    const bool lambertPath = getenv("PBRTGPU_HOSTSIM_LAMBERT") && atoi(getenv("PBRTGPU_HOSTSIM_LAMBERT")) != 0;
     int64_t totals[4] = {0, 0, 0, 0};
     for (int s0 = pl.sppBegin; s0 < pl.sppEnd; s0 += pl.sppChunk) {
         w.sppBegin = s0;
@@ -210,7 +211,12 @@ extern "C" int hostsim_render(void *p, const pbrtgpu_render_params *rp, float *f
                 parallelFor(cnt.nHit[d], threads, [&](int64_t a, int64_t b) { 
                     for (int64_t i = a; i < b; ++i) {
                         if (w.integrator == PBRTGPU_INTEGRATOR_DIRECT) stageShadeDirect(w, d, cur, w.hitIdx[i]);
-                        else stageShade(w, d, cur, w.hitIdx[i]);
+                        else if (lambertPath) {  // as the CUDA driver does: single-Lambert-lobe materials through the Lambert instantiation
+                            int prim = f2i(w.hits[w.hitIdx[i]].x);
+                            int m = w.sc.primMaterial ? w.sc.primMaterial[prim] : -1;
+                            if (m < 0 || w.sc.matLobes[m].shadeClass == 0) stageShadeLambert(w, d, cur, w.hitIdx[i]);
+                            else stageShade(w, d, cur, w.hitIdx[i]);
+                        } else stageShade(w, d, cur, w.hitIdx[i]);
                     }
                 });
                 parallelFor(cnt.nShadow[d], threads, [&](int64_t a, int64_t b) {

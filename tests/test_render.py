@@ -274,7 +274,8 @@ def test_gpu_shards_add_up(pkg, gpu, golden):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("knob", ["PBRTGPU_SORT_HITS=0", "PBRTGPU_SHADE_BLOCK=1024", "PBRTGPU_SHADE_SYNC=0"])
+@pytest.mark.parametrize("knob", ["PBRTGPU_SORT_HITS=0", "PBRTGPU_SHADE_BLOCK=1024", "PBRTGPU_SHADE_SYNC=0", "PBRTGPU_SHADE_LAMBERT=0",
+                                  "PBRTGPU_LAMBERT_BLOCK=2562"])
 def test_gpu_scheduling_knobs_do_not_change_the_image(pkg, gpu, monkeypatch, knob):
     """How vertices are mapped to threads -- the hit queue split by material class, the shade block shape, phase
     barriers or none -- must not change any path: only the order of float atomics into a film pixel may differ."""
@@ -462,3 +463,16 @@ def test_one_ulp_of_libm_moves_killeroo_samples(pkg, hostsim_lib, hostsim_pertur
     # B200, same scene at 960 x 540: 0.11 % of the samples move by more than 1e-3 relative (gpurun_out/r02c_diff.log)
     assert 1e-4 < moved < 1e-2, (moved, s)
     assert s["mean_rel"] < 2e-4, s  # unbiased: flips go both ways
+
+
+@pytest.mark.parametrize("case", ["box_glass", "portal_room_portal", "null_shells", "sphere_lights"])
+def test_lambert_shade_instantiation_is_bit_identical(pkg, hostsim_lib, case, monkeypatch):
+    """stageShadePhased<..., LAMBERT> (bsdf_eval.h: lambertF / lambertPdf / lambertSampleF) against the general BSDF
+    routines on the same vertices: one thread, so that even the order of additions into a pixel is the same -- the two
+    films must be equal bit for bit."""
+    hs = load_case(pkg, case)
+    _, general, st0 = util.hostsim_render(hostsim_lib, hs, threads=1)
+    monkeypatch.setenv("PBRTGPU_HOSTSIM_LAMBERT", "1")
+    _, lambert, st1 = util.hostsim_render(hostsim_lib, hs, threads=1)
+    assert list(st0) == list(st1)
+    assert np.array_equal(util.bits(general), util.bits(lambert))

@@ -12,7 +12,12 @@ import bench
 pk = importlib.import_module("pbrt-v3-light-portals_b200")
 
 
+ONLY = [a.lower() for a in sys.argv[1:]]  # optional substrings: run only the configurations whose name contains one of them
+
+
 def run(name, text, base_dir, repeats=3):
+    if ONLY and not any(o in name.lower() for o in ONLY):
+        return
     hs = pk.HostScene(text=text, base_dir=base_dir)
     ctx = pk.GpuContext(0)
     ctx.upload(hs)

@@ -16,6 +16,11 @@
 //       any     -> out.bin: n x uint8
 //       prints one JSON line with the Mrays/s of BVHAccel::Intersect(P) run
 //       inside the reference's ParallelFor.
+//   ref_harness halton    scene.pbrt queries.bin out.bin
+//       the scene's own Sampler "halton" (built by MakeSampler over the film's sample bounds, halton.cpp:65-139).
+//       queries.bin: n x {int32 x, int32 y, int32 dim, int32 count, int64 sampleNum}.
+//       count == 0 -> one float: HaltonSampler::SampleDimension(GetIndexForSample(sampleNum), dim) at pixel (x, y);
+//       count  > 0 -> `count` floats: StartPixel, SetSampleNumber(sampleNum), then Get1D() `count` times (`dim` unused).
 //
 // origId is the index of the primitive in RenderOptions::primitives BEFORE
 // the BVH reorders them (api.cpp:1380-1436), i.e. creation order.
@@ -176,7 +181,42 @@ static void harnessIntersect(const Scene &scene,
            (long long)n, sec, n / sec / 1e6, gThreads, gMode.c_str());
 }
 
+static void harnessHalton() {
+    std::unique_ptr<Camera> camera(renderOptions->MakeCamera());
+    std::shared_ptr<Sampler> sampler = MakeSampler(renderOptions->SamplerName, renderOptions->SamplerParams, camera->film);
+    HaltonSampler *hs = dynamic_cast<HaltonSampler *>(sampler.get());
+    if (!hs) { fprintf(stderr, "the scene's sampler is not \"halton\"\n"); exit(1); }
+    struct Query { int32_t x, y, dim, count; int64_t num; };
+    std::vector<Query> q;
+    {
+        FILE *f = fopen(gRays.c_str(), "rb");
+        if (!f) { fprintf(stderr, "cannot open %s\n", gRays.c_str()); exit(1); }
+        Query one;
+        while (fread(&one, sizeof(one), 1, f) == 1) q.push_back(one);
+        fclose(f);
+    }
+    FILE *f = fopen(gOutA.c_str(), "wb");
+    for (const Query &k : q) {
+        hs->StartPixel(Point2i(k.x, k.y));
+        hs->SetSampleNumber(k.num);
+        if (k.count == 0) {
+            float v = hs->SampleDimension(hs->GetIndexForSample(k.num), k.dim);
+            fwrite(&v, 4, 1, f);
+        } else
+            for (int i = 0; i < k.count; ++i) {
+                float v = hs->Get1D();
+                fwrite(&v, 4, 1, f);
+            }
+    }
+    fclose(f);
+}
+
 void pbrtWorldEnd() {
+    if (gCommand == "halton") {
+        harnessHalton();
+        fflush(stdout);
+        _exit(0);
+    }
     std::map<const Primitive *, int> origId;
     for (size_t i = 0; i < renderOptions->primitives.size(); ++i)
         origId[renderOptions->primitives[i].get()] = (int)i;
@@ -200,7 +240,8 @@ int main(int argc, char **argv) {
         fprintf(stderr,
                 "usage: ref_harness dump scene.pbrt out_prefix\n"
                 "       ref_harness intersect scene.pbrt rays.bin out.bin "
-                "closest|any [nthreads]\n");
+                "closest|any [nthreads]\n"
+                "       ref_harness halton scene.pbrt queries.bin out.bin\n");
         return 2;
     }
     gCommand = argv[1];
@@ -209,6 +250,9 @@ int main(int argc, char **argv) {
     options.quiet = true;
     if (gCommand == "dump") {
         gOutA = argv[3];
+    } else if (gCommand == "halton" && argc >= 5) {
+        gRays = argv[3];
+        gOutA = argv[4];
     } else if (gCommand == "intersect" && argc >= 6) {
         gRays = argv[3];
         gOutA = argv[4];

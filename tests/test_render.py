@@ -204,6 +204,45 @@ def test_halton_scrambled_digits_against_bigint_restatement(pkg, hostsim_lib):
             assert got == want, (dim, b, got, want)
 
 
+def _halton_reference():
+    """tests/golden/halton_reference.npz: the reference's own HaltonSampler, dumped by oracle/_ref/ref_harness
+    (tests/golden/make_golden_halton.py)."""
+    sys.path.insert(0, GOLDEN)
+    import make_golden_halton as mk
+    g = np.load(os.path.join(GOLDEN, "halton_reference.npz"))
+    q, s = mk.queries()
+    assert np.array_equal(q, g["q"]) and np.array_equal(s, g["s"])  # the committed queries are the seeded ones
+    return q, g["q_value"], s, g["s_value"]
+
+
+def _check_halton_against_reference(pkg, sample):
+    """sample(params, xy, num, dim) -> float32 values of the code under test.  Row a1's direct pin: SampleDimension at 20 000
+    (pixel, sample number, dimension) triples, Halton indices up to 5e9, and the first 96 values of 64 Get1D() streams
+    (for a path render no sample arrays are requested, so the k-th Get1D() is dimension k), bit for bit."""
+    hs = load_case(pkg, "box_glass")
+    q, qv, s, sv = _halton_reference()
+    xy = np.ascontiguousarray(np.stack([q["x"], q["y"]], 1).astype(np.int32))
+    got = sample(hs.params, xy, np.ascontiguousarray(q["num"]), np.ascontiguousarray(q["dim"]))
+    assert np.array_equal(util.bits(got), util.bits(qv)), "SampleDimension differs from the reference's HaltonSampler"
+    k = sv.shape[1]
+    xy = np.ascontiguousarray(np.repeat(np.stack([s["x"], s["y"]], 1), k, axis=0).astype(np.int32))
+    num = np.ascontiguousarray(np.repeat(s["num"], k))
+    dim = np.ascontiguousarray(np.tile(np.arange(k, dtype=np.int32), len(s)))
+    got = sample(hs.params, xy, num, dim)
+    assert np.array_equal(util.bits(got), util.bits(sv.reshape(-1))), "Get1D stream differs from the reference's HaltonSampler"
+
+
+def test_halton_matches_the_reference_sampler_cpu_stepped(pkg, hostsim_lib):
+    import ctypes as C
+
+    def sample(params, xy, num, dim):
+        out = np.zeros(len(num), np.float32)
+        hostsim_lib.hostsim_halton(C.byref(params), xy.ctypes.data_as(C.c_void_p), num.ctypes.data_as(C.c_void_p),
+                                   dim.ctypes.data_as(C.c_void_p), C.c_int64(len(num)), out.ctypes.data_as(C.c_void_p))
+        return out
+    _check_halton_against_reference(pkg, sample)
+
+
 # ---------------------------------------------------------------- GPU
 
 @pytest.mark.gpu
@@ -256,6 +295,19 @@ def test_gpu_halton_matches_cpu_stepped_code(pkg, gpu, hostsim_lib):
     hostsim_lib.hostsim_halton(C.byref(hs.params), xy.ctypes.data_as(C.c_void_p), num.ctypes.data_as(C.c_void_p),
                                dim.ctypes.data_as(C.c_void_p), C.c_int64(n), out_c.ctypes.data_as(C.c_void_p))
     assert np.array_equal(util.bits(out_g), util.bits(out_c))  # integer digit arithmetic: bit-exact
+
+
+@pytest.mark.gpu
+def test_gpu_halton_matches_the_reference_sampler(pkg, gpu):
+    """The CUDA sampler against values dumped from the reference's own HaltonSampler (not against this repository's CPU build)."""
+    import ctypes as C
+    lib = pkg.gpu_lib()
+
+    def sample(params, xy, num, dim):
+        out = np.zeros(len(num), np.float32)
+        assert lib.pbrtgpu_halton_samples(gpu._h, C.byref(params), xy.ctypes.data, num.ctypes.data, dim.ctypes.data, len(num), out.ctypes.data) == 0
+        return out
+    _check_halton_against_reference(pkg, sample)
 
 
 @pytest.mark.gpu

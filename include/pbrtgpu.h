@@ -74,7 +74,10 @@ enum {
 /* PortalStrategy, lights/portal_arealight.h:12 (same numbering) */
 enum { PBRTGPU_PORTAL_UNIFORM_PORTAL = 0, PBRTGPU_PORTAL_UNIFORM_LIGHT = 1, PBRTGPU_PORTAL_PROJECTION = 2,
        /* not in the reference: solid-angle sampling of the portal rectangle, alone / one-sample MIS with the BSDF (device/portal.h) */
-       PBRTGPU_PORTAL_SOLIDANGLE = 3, PBRTGPU_PORTAL_SOLIDANGLE_MIS = 4 };
+       PBRTGPU_PORTAL_SOLIDANGLE = 3, PBRTGPU_PORTAL_SOLIDANGLE_MIS = 4,
+       /* portal / BSDF / light-area sampling combined with the fork's PowerHeuristic3 (sampling.h:177-180), AAPortal::InFrustum
+          (aaportal.cpp:101-112, disabled in the reference) re-enabled as a cull of the portal technique */
+       PBRTGPU_PORTAL_SOLIDANGLE_MIS3 = 5 };
 
 #define PBRTGPU_PLANE_STRIDE 48  /* floats per AAPlaneShape: lo[3] hi[3] ax facingFw area pad[7] O2W[16] W2O[16]   shapes/plane.h:12-40 */
 #define PBRTGPU_SPHERE_STRIDE 48 /* floats per Sphere: radius zMin zMax thetaMin thetaMax phiMax pad[10] O2W[16] W2O[16]  shapes/sphere.h */

@@ -128,6 +128,7 @@ PG_HD float powerHeuristic(float fPdf, float gPdf) {  // PowerHeuristic(1, f, 1,
 //   solidangle      the direction is drawn through a portal:  f |cos| Le / p_A
 //   solidangle_mis  one-sample MIS (Veach 9.2.4) of that technique and BSDF sampling, each taken with
 //                   probability 1/2, balance heuristic:       f |cos| Le / (p_A / 2 + p_B / 2)
+//   solidangle_mis3 portal, BSDF and light-area sampling under PowerHeuristic3, AAPortal::InFrustum re-enabled (below)
 // u1 = the scattering sample, u2 = the light sample of UniformSampleOneLight / AllLights.
 PG_HD_NOINLINE bool estimateDirectPortalSolidAngle(const DevScene &sc, int li, int strat, const float *lightRec, const float *portals, int nPortals,
                                                    const SurfInt &it, const BSDF &bsdf, float u1x, float u1y, float u2x, float u2y, Spec scale,
@@ -136,6 +137,54 @@ PG_HD_NOINLINE bool estimateDirectPortalSolidAngle(const DevScene &sc, int li, i
     M44 o2w = loadM44(lightRec + 16), w2o = loadM44(lightRec + 32);
     int sel;
     SphRect rect;
+    if (strat == PBRTGPU_PORTAL_SOLIDANGLE_MIS3) {
+        // Three techniques -- A: a direction through a portal, uniform in solid angle (portals that fail AAPortal's frustum
+        // test left out); B: BSDF sampling; L: a point of the light, uniform in area (Shape::Sample(ref, u), shape.cpp:56-77)
+        // -- one of them drawn per vertex with equal probability c (one-sample model, Veach 9.2.4) and weighted with the
+        // fork's PowerHeuristic3 (sampling.h:177-180; the equal c cancel): w_i = p_i^2 / (p_A^2 + p_B^2 + p_L^2), estimate
+        // w_i f |cos| Le / (c p_i).  Where no portal is usable (behind all of them, outside every frustum) only B and L remain.
+        PlaneParams lightPl = loadPlane(lightRec);
+        float sumOmega = portalSolidAngles(portals, nPortals, o2w, w2o, it.p, u2x, &sel, &rect, &lightPl);
+        const bool haveA = sumOmega > 0 && sel >= 0;
+        const float pAin = haveA ? 1 / sumOmega : 0.f;
+        const int nTech = haveA ? 3 : 2;
+        int tech = (int)(u2y * nTech);
+        if (tech > nTech - 1) tech = nTech - 1;
+        tech += haveA ? 0 : 1;  // 0 = A, 1 = B, 2 = L
+        V3 wi = v3(0, 0, 0);
+        Spec f;
+        float pA = 0, pB = 0, pL = 0;
+        if (tech == 0) {
+            wi = normalize(sphRectSample(rect, u1x, u1y) - it.p);
+            pA = pAin;
+        } else if (tech == 1) {
+            int sampledType;
+            f = bsdfSampleF(bsdf, it.wo, &wi, u1x, u1y, &pB, flagsNS, &sampledType);
+            if (isBlack(f) || !(pB > 0)) return true;
+        } else {
+            ShapeSample pLs;
+            Spec Li = lightSampleLi(sc, li, it, u1x, u1y, &wi, &pL, &pLs);
+            if (isBlack(Li) || !(pL > 0)) return true;
+        }
+        if (tech != 1) {
+            f = bsdfF(bsdf, it.wo, wi, flagsNS);
+            pB = bsdfPdf(bsdf, it.wo, wi, flagsNS);
+        }
+        f *= absDot(wi, it.ns);
+        if (isBlack(f)) return true;
+        if (tech != 0) pA = (haveA && portalsContainDirection(portals, nPortals, o2w, w2o, it.p, wi, &lightPl)) ? pAin : 0.f;
+        if (tech != 2) pL = lightPdfLi(sc, li, it, wi);
+        float pSel = tech == 0 ? pA : (tech == 1 ? pB : pL);
+        float denom = pA * pA + pB * pB + pL * pL;
+        if (!(pSel > 0) || !(denom > 0)) return true;
+        float weight = (pSel * pSel) / denom;  // PowerHeuristic3(1, pSel, 1, ., 1, .)
+        out->hasClosest = true;
+        out->closestRay = spawnRay(it.p, it.pError, it.n, wi);
+        out->closestContrib = scale * (f * (weight * (float)nTech / pSel));
+        out->light = li;
+        out->mode = NEE_MIS_LIGHT;
+        return true;
+    }
     float sumOmega = portalSolidAngles(portals, nPortals, o2w, w2o, it.p, u2x, &sel, &rect);
     if (!(sumOmega > 0) || sel < 0) return false;  // behind every portal: the caller falls back to sampling the light
     const float pA = 1 / sumOmega;
@@ -181,7 +230,7 @@ PG_HD_NOINLINE void estimateDirectPortal(const DevScene &sc, int li, const SurfI
     int pBegin = PG_LD(sc.lightPortalBegin + li), nPortals = PG_LD(sc.lightPortalBegin + li + 1) - pBegin;
     const float *portals = sc.portalParams + PBRTGPU_PORTAL_STRIDE * (size_t)pBegin;
     M44 w2o = loadM44(lightRec + 32);
-    if (strat == PBRTGPU_PORTAL_SOLIDANGLE || strat == PBRTGPU_PORTAL_SOLIDANGLE_MIS) {
+    if (strat >= PBRTGPU_PORTAL_SOLIDANGLE) {
         if (EXT && nPortals > 0 && estimateDirectPortalSolidAngle(sc, li, strat, lightRec, portals, nPortals, it, bsdf, u1x, u1y, u2x, u2y, scale, out)) return;
         strat = PBRTGPU_PORTAL_UNIFORM_LIGHT;  // behind every portal
     }

@@ -178,14 +178,49 @@ PG_HD bool rectContainsDirection(V3 s, V3 ex, V3 ey, V3 o, V3 wi) {
     return a >= 0 && a <= 1 && b >= 0 && b <= 1;
 }
 
+// AAPortal's viewing frustum (aaportal.cpp:14-57, 101-112): four planes, each through one edge of the portal and the
+// OPPOSITE edge of the light (spanned by the two diagonals corner-of-portal minus opposite-corner-of-light that end on
+// that edge) -- outside it no point of the light is seen through the portal.  The reference builds the planes and then
+// disables the test (`return true;`, Q1).  It is used here only by the strategy "solidangle_mis3", as a cull of the
+// portal TECHNIQUE inside a multiple-importance combination whose other two techniques cover every direction: a portal
+// that fails the test is neither sampled nor counted in the portal pdf, so the test cannot bias the estimate, it only
+// stops samples from being spent on portals that cannot show the light.  Everything is evaluated in the light's object
+// space (the reference mixes the portal's object-space corners with a world-space point; its scenes' transforms are
+// identities).
+PG_HD V3 aaplaneCorner(const PlaneParams &pl, int k) {  // AAPlaneShape::V0..V3, plane.cpp:85-107
+    V3 v = pl.lo;
+    if (k == 1 || k == 2) v.set(pl.ax1, pl.hi[pl.ax1]);
+    if (k == 2 || k == 3) v.set(pl.ax0, pl.hi[pl.ax0]);
+    if (k == 2) v = pl.hi;
+    return v;
+}
+PG_HD_NOINLINE bool portalInFrustum(const PortalRec &po, const PlaneParams &light, const M44 &lightW2O, V3 p) {
+    V3 q = xformPoint(lightW2O, p);
+    V3 fd[4], pc[4];
+    for (int k = 0; k < 4; ++k) {
+        pc[k] = aaplaneCorner(po.pl, k);
+        fd[k] = normalize(pc[k] - aaplaneCorner(light, (k + 2) & 3));
+    }
+    bool res = true;
+    for (int k = 0; k < 4; ++k) {
+        int k1 = (k + 1) & 3;
+        V3 fn = po.pl.facingFw ? cross(fd[k], fd[k1]) : cross(fd[k1], fd[k]);
+        V3 fp = (pc[k] + pc[k1]) / 2;
+        res &= dot(fp - q, fn) >= 0;
+    }
+    return res;
+}
+
 // Solid angles of the portals in front of p; returns their sum.  With `pick` in [0, 1): *sel = the portal drawn
 // with probability omega_i / sum and *rect = its spherical rectangle.
+// `frustumOf` != nullptr (the light's own plane): portals whose viewing frustum does not hold p are left out as well.
 PG_HD_NOINLINE float portalSolidAngles(const float *portals, int nPortals, const M44 &lightO2W, const M44 &lightW2O, V3 p, float pick, int *sel,
-                                       SphRect *rect) {
+                                       SphRect *rect, const PlaneParams *frustumOf = nullptr) {
     float sum = 0;
     for (int i = 0; i < nPortals; ++i) {
         PortalRec po = loadPortal(portals + PBRTGPU_PORTAL_STRIDE * i);
         if (!portalInFront(po, lightW2O, p)) continue;
+        if (frustumOf && !portalInFrustum(po, *frustumOf, lightW2O, p)) continue;
         V3 s, ex, ey;
         portalWorldRect(po, lightO2W, &s, &ex, &ey);
         sum += sphRectInit(s, ex, ey, p).S;
@@ -196,6 +231,7 @@ PG_HD_NOINLINE float portalSolidAngles(const float *portals, int nPortals, const
     for (int i = 0; i < nPortals; ++i) {
         PortalRec po = loadPortal(portals + PBRTGPU_PORTAL_STRIDE * i);
         if (!portalInFront(po, lightW2O, p)) continue;
+        if (frustumOf && !portalInFrustum(po, *frustumOf, lightW2O, p)) continue;
         V3 s, ex, ey;
         portalWorldRect(po, lightO2W, &s, &ex, &ey);
         SphRect q = sphRectInit(s, ex, ey, p);
@@ -208,10 +244,12 @@ PG_HD_NOINLINE float portalSolidAngles(const float *portals, int nPortals, const
     return sum;
 }
 // is wi (from p) inside one of the portals in front of p?
-PG_HD bool portalsContainDirection(const float *portals, int nPortals, const M44 &lightO2W, const M44 &lightW2O, V3 p, V3 wi) {
+PG_HD bool portalsContainDirection(const float *portals, int nPortals, const M44 &lightO2W, const M44 &lightW2O, V3 p, V3 wi,
+                                   const PlaneParams *frustumOf = nullptr) {
     for (int i = 0; i < nPortals; ++i) {
         PortalRec po = loadPortal(portals + PBRTGPU_PORTAL_STRIDE * i);
         if (!portalInFront(po, lightW2O, p)) continue;
+        if (frustumOf && !portalInFrustum(po, *frustumOf, lightW2O, p)) continue;
         V3 s, ex, ey;
         portalWorldRect(po, lightO2W, &s, &ex, &ey);
         if (rectContainsDirection(s, ex, ey, p, wi)) return true;

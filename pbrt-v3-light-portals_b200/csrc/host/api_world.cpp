@@ -319,6 +319,7 @@ void SceneApi::Shape(const std::string &name, const ParamSet &params) {
                 else if (st == "projection") l.strategy = PBRTGPU_PORTAL_PROJECTION;
                 else if (st == "solidangle") l.strategy = PBRTGPU_PORTAL_SOLIDANGLE;  // the two strategies the reference does not have
                 else if (st == "solidangle_mis") l.strategy = PBRTGPU_PORTAL_SOLIDANGLE_MIS;
+                else if (st == "solidangle_mis3") l.strategy = PBRTGPU_PORTAL_SOLIDANGLE_MIS3;
                 else {
                     hostWarning("AAPortal strategy unknown");
                     l.strategy = PBRTGPU_PORTAL_UNIFORM_LIGHT;  // the reference leaves it uninitialised

@@ -303,3 +303,21 @@ extern "C" int hostsim_halton(const pbrtgpu_render_params *rp, const int32_t *xy
         out[i] = haltonSample(h, haltonPixelOffset(h, xy[2 * i], xy[2 * i + 1]) + num[i] * h.sampleStride, dim[i]);
     return 0;
 }
+
+// AAPortal::InFrustum as portal.h restates it (strategy "solidangle_mis3"), for the geometric test against brute-force
+// visibility: out[i] = 1 if points[3i..] lies in the viewing frustum of portal `portal` of light `light`.
+extern "C" int hostsim_portal_in_frustum(const pbrtgpu_scene *s, int light, int portal, const float *points, int64_t n, uint8_t *out) {
+    if (light < 0 || light >= s->n_lights || s->light_tag[light] != PBRTGPU_LIGHT_PORTAL_AREA) return -1;
+    int slot = s->light_prim[light];
+    const float *lightRec = s->plane_params + PBRTGPU_PLANE_STRIDE * (size_t)s->prim_shape[slot];
+    int pb = s->light_portal_begin[light];
+    if (portal < 0 || pb + portal >= s->light_portal_begin[light + 1]) return -1;
+    PortalRec po = loadPortal(s->portal_params + PBRTGPU_PORTAL_STRIDE * (size_t)(pb + portal));
+    PlaneParams lp = loadPlane(lightRec);
+    M44 w2o = loadM44(lightRec + 32);
+    for (int64_t i = 0; i < n; ++i) {
+        bool front = portalInFront(po, w2o, v3(points[3 * i], points[3 * i + 1], points[3 * i + 2]));
+        out[i] = (front ? 2 : 0) | (portalInFrustum(po, lp, w2o, v3(points[3 * i], points[3 * i + 1], points[3 * i + 2])) ? 1 : 0);
+    }
+    return 0;
+}

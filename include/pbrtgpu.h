@@ -205,6 +205,18 @@ const char *pbrtgpu_last_error(const pbrtgpu_ctx *ctx); /* ctx may be NULL: last
 
 int pbrtgpu_upload_scene(pbrtgpu_ctx *ctx, const pbrtgpu_scene *scene);
 
+/* BVHAccel::HLBVHBuild on the device (accelerators/bvh.cpp:404-638: Morton codes :107-137, 411-428; the stable LSD radix
+ * sort :139-180; one emitLBVH treelet per 12-bit Morton prefix :433-455, 474-536; the SAH tree over the treelet roots
+ * :538-638, which stays on the host; flattenBVHTree :640-658).  prim_bounds: n*6 world bounds {pMin.xyz pMax.xyz} in creation
+ * order (Primitive::WorldBound).  Results, in the reference's flattened form: the LinearBVHNode arrays (node_capacity >= 2 n
+ * entries each, *n_nodes_out used) and ordered_prims[slot] = creation-order number of the primitive in BVH slot `slot`.
+ * The tree equals the reference's (and pbrthost's host build with "splitmethod" "hlbvh") node for node; leaf slots are numbered
+ * as the reference numbers them with --nthreads 1.  elapsed_ms (may be NULL): CUDA-event time of the build kernels.
+ * The signature is pbrthost.h's pbrthost_hlbvh_builder with `user` = ctx. */
+int pbrtgpu_build_hlbvh(pbrtgpu_ctx *ctx, const float *prim_bounds, int32_t n, int32_t max_prims_in_node, int32_t node_capacity,
+                        float *bvh_bounds, int32_t *bvh_offset, uint16_t *bvh_nprims, uint8_t *bvh_axis, int32_t *ordered_prims,
+                        int32_t *n_nodes_out, float *elapsed_ms);
+
 /* BVHAccel::Intersect / IntersectP on a ray batch (accelerators/bvh.cpp:662-738).
  * rays: n*8 floats {ox,oy,oz,tMax,dx,dy,dz,pad}.  Host-buffer forms copy in
  * and out; the _device forms work on device pointers and report the kernel's
@@ -262,6 +274,12 @@ int pbrtgpu_set_stream(pbrtgpu_ctx *ctx, void *cuda_stream);
 int pbrtgpu_halton_samples(pbrtgpu_ctx *ctx, const pbrtgpu_render_params *params,
                            const int32_t *pixel_xy, const int64_t *sample_num, const int32_t *dim,
                            int64_t n, float *out); /* HaltonSampler::SampleDimension */
+
+/* The device layout of the uploaded scene -- 64-byte two-child records (n_records = interior nodes + 1) and 48-byte
+ * primitive slots, csrc/device/bvh.h -- copied back, so that the conversion kernels run by pbrtgpu_upload_scene can be
+ * compared byte for byte with the host restatement (PBRTGPU_LAYOUT=host). */
+int pbrtgpu_debug_read_layout(pbrtgpu_ctx *ctx, float *nodes /* n_records*16 */, int64_t n_records, float *tris /* n_prims*12 */,
+                              int64_t n_prims);
 
 #ifdef __cplusplus
 }

@@ -40,6 +40,19 @@ void pbrthost_set_spp(pbrthost_scene *s, int spp);
 int pbrthost_film_to_rgb(const pbrthost_scene *s, const float *film_xyzw, float *rgb);
 int pbrthost_write_image(const pbrthost_scene *s, const char *filename, const float *rgb);
 
+/* Accelerator "bvh" "string splitmethod" "hlbvh" can be built by someone else: a function with the signature of
+ * pbrtgpu_build_hlbvh (pbrtgpu.h; `user` = its ctx) replaces the host's HLBVHBuild for every scene loaded afterwards.  The library
+ * itself stays free of GPU state -- an embedding application connects the two:
+ *     pbrthost_set_hlbvh_builder((pbrthost_hlbvh_builder)pbrtgpu_build_hlbvh, ctx);
+ * fn == NULL restores the host build.  A builder that fails makes the load fail (no silent fallback).  The other split
+ * methods are always built on the host. */
+typedef int (*pbrthost_hlbvh_builder)(void *user, const float *prim_bounds, int32_t n, int32_t max_prims_in_node, int32_t node_capacity,
+                                      float *bvh_bounds, int32_t *bvh_offset, uint16_t *bvh_nprims, uint8_t *bvh_axis, int32_t *ordered_prims,
+                                      int32_t *n_nodes_out, float *elapsed_ms);
+void pbrthost_set_hlbvh_builder(pbrthost_hlbvh_builder fn, void *user);
+/* Wall-clock milliseconds the last load spent building its BVH, and the builder's own device time (0 for a host build). */
+void pbrthost_last_bvh_build_ms(double *wall_ms, float *builder_ms);
+
 /* Host-side pieces exposed for parity tests. */
 int pbrthost_halton_permutations(uint16_t *out, int64_t n); /* ComputeRadicalInversePermutations, lowdiscrepancy.cpp:2490-2504; n = 3682913 */
 

@@ -126,6 +126,10 @@ def host_lib():
         lib.pbrthost_film_to_rgb.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         lib.pbrthost_write_image.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p]
         lib.pbrthost_halton_permutations.argtypes = [C.c_void_p, C.c_int64]
+        lib.pbrthost_set_hlbvh_builder.argtypes = [C.c_void_p, C.c_void_p]
+        lib.pbrthost_set_hlbvh_builder.restype = None
+        lib.pbrthost_last_bvh_build_ms.argtypes = [_p(C.c_double), _p(C.c_float)]
+        lib.pbrthost_last_bvh_build_ms.restype = None
         _host = lib
     return _host
 
@@ -148,6 +152,9 @@ def gpu_lib():
         lib.pbrtgpu_intersect_closest_device.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, _p(C.c_float)]
         lib.pbrtgpu_intersect_any_device.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, _p(C.c_float)]
         lib.pbrtgpu_set_stream.argtypes = [C.c_void_p, C.c_void_p]
+        lib.pbrtgpu_debug_read_layout.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64]
+        lib.pbrtgpu_build_hlbvh.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p,
+                                            C.c_void_p, C.c_void_p, _p(C.c_int32), _p(C.c_float)]
         if hasattr(lib, "pbrtgpu_intersect_closest_noalloc"):
             lib.pbrtgpu_intersect_closest_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]
         if hasattr(lib, "pbrtgpu_render"):
@@ -214,6 +221,13 @@ class HostScene:
             raise PbrtGpuError("write_image(%s) failed" % filename)
 
 
+def last_bvh_build_ms():
+    """(wall ms, builder's device ms) of the BVH build of the scene loaded last."""
+    w, b = C.c_double(0), C.c_float(0)
+    host_lib().pbrthost_last_bvh_build_ms(C.byref(w), C.byref(b))
+    return w.value, b.value
+
+
 def halton_permutations():
     out = np.empty(N_HALTON_PERMS, np.uint16)
     if host_lib().pbrthost_halton_permutations(out.ctypes.data, N_HALTON_PERMS) != 0:
@@ -247,6 +261,33 @@ class GpuContext:
     def upload(self, scene):
         view = scene.view if isinstance(scene, HostScene) else scene
         self._check(self._lib.pbrtgpu_upload_scene(self._h, C.byref(view)))
+
+    def build_hlbvh(self, prim_bounds, max_prims_in_node=4):
+        """BVHAccel::HLBVHBuild on the device.  prim_bounds: (n, 6) world bounds in creation order.  Returns (bounds (m, 6),
+        offset, nprims, axis, ordered_prims, device_ms): the LinearBVHNode arrays and the primitive order."""
+        pb = np.ascontiguousarray(prim_bounds, dtype=np.float32).reshape(-1, 6)
+        n = len(pb)
+        cap = 2 * n
+        bounds, offset = np.zeros((cap, 6), np.float32), np.zeros(cap, np.int32)
+        nprims, axis, order = np.zeros(cap, np.uint16), np.zeros(cap, np.uint8), np.zeros(n, np.int32)
+        m, ms = C.c_int32(0), C.c_float(0)
+        self._check(gpu_lib().pbrtgpu_build_hlbvh(self._h, pb.ctypes.data, n, max_prims_in_node, cap, bounds.ctypes.data, offset.ctypes.data,
+                                                  nprims.ctypes.data, axis.ctypes.data, order.ctypes.data, C.byref(m), C.byref(ms)))
+        return bounds[:m.value], offset[:m.value], nprims[:m.value], axis[:m.value], order, ms.value
+
+    def read_layout(self, scene):
+        """The device layout of the uploaded scene as (records (m, 16) uint32, slots (n, 12) uint32)."""
+        v = scene.view
+        m = 1 + int((np.asarray(v.array("bvh_nprims", v.n_nodes)) == 0).sum())
+        nodes, tris = np.zeros((m, 16), np.float32), np.zeros((v.n_prims, 12), np.float32)
+        self._check(gpu_lib().pbrtgpu_debug_read_layout(self._h, nodes.ctypes.data, m, tris.ctypes.data, v.n_prims))
+        return nodes.view(np.uint32), tris.view(np.uint32)
+
+    def install_hlbvh_builder(self, on=True):
+        """Scenes loaded from now on with Accelerator "bvh" "string splitmethod" "hlbvh" get their tree from this GPU
+        (pbrthost_set_hlbvh_builder); on=False restores the host build."""
+        fn = C.cast(gpu_lib().pbrtgpu_build_hlbvh, C.c_void_p) if on else None
+        host_lib().pbrthost_set_hlbvh_builder(fn, self._h if on else None)
 
     def set_stream(self, cuda_stream_ptr):
         self._check(self._lib.pbrtgpu_set_stream(self._h, C.c_void_p(cuda_stream_ptr)))

@@ -59,6 +59,9 @@ struct pbrtgpu_ctx {
     // render scratch, grown on demand
     pg::DeviceBuffer scratch[16];
     pg::DeviceBuffer film;
+    pg::DeviceBuffer layoutScratch;  // raw node / primitive arrays of the upload in progress (layout_device.cu), kept for the next one
+    long long nWideRecords = 0;      // interior records of the uploaded scene, the synthetic root parent included
+    bool layoutOnDevice = true;      // PBRTGPU_LAYOUT=host: build the device layout with layout_build.h on the CPU instead
     void *filmTarget = nullptr;  // pbrtgpu_render_device_into: the caller's device film for the render in progress (else `film`)
     bool asyncRender = false;    // ... and, without a stats request, no host synchronisation at the end of the render
     int smCount = 148;
@@ -101,6 +104,20 @@ struct pbrtgpu_ctx {
 
 namespace pg {
 int ensureBuffer(pbrtgpu_ctx *ctx, DeviceBuffer &b, size_t bytes);
+// a device array that belongs to the uploaded scene: taken from the previous scene's arrays when a size matches
+inline int allocSceneArray(pbrtgpu_ctx *ctx, size_t bytes, void **out) {
+    void *d = nullptr;
+    for (size_t i = 0; i < ctx->scenePool.size(); ++i)
+        if (ctx->scenePool[i].bytes == bytes) {
+            d = ctx->scenePool[i].p;
+            ctx->scenePool.erase(ctx->scenePool.begin() + i);
+            break;
+        }
+    if (!d) PG_CUDA(ctx, cudaMalloc(&d, bytes));
+    ctx->sceneAllocs.push_back({d, bytes});
+    *out = d;
+    return PBRTGPU_OK;
+}
 template <typename T>
 int uploadArray(pbrtgpu_ctx *ctx, const T *host, size_t count, const T **dev) {
     *dev = nullptr;

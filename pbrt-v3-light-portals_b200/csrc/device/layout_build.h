@@ -18,7 +18,7 @@ namespace pg {
 // Is this triangle one that Triangle::Intersect rejects after the hit test
 // (degenerate partial derivatives AND zero-area geometry, triangle.cpp:294-317)?
 // Depends only on the vertices and uvs, so it is decided once here.
-inline bool triangleIsDegenerate(const float *p, const float *uvOrNull) {
+PG_HD bool triangleIsDegenerate(const float *p, const float *uvOrNull) {
     V3 p0 = v3(p[0], p[1], p[2]), p1 = v3(p[3], p[4], p[5]), p2 = v3(p[6], p[7], p[8]);
     float uv[3][2] = {{0, 0}, {1, 0}, {1, 1}};  // Triangle::GetUVs default, triangle.h:114-123
     if (uvOrNull)

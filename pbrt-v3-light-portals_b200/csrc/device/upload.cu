@@ -15,6 +15,11 @@ using namespace pg;
 static std::string gCreateError;
 
 namespace pg {
+int buildLayoutOnDevice(pbrtgpu_ctx *ctx, const pbrtgpu_scene *s, int nInterior, const float *d_triUV, const unsigned char *d_primFlags,
+                        F4 *d_nodes, F4 *d_tris, int *firstBadHost);
+}
+
+namespace pg {
 int ensureBuffer(pbrtgpu_ctx *ctx, DeviceBuffer &b, size_t bytes) {
     if (b.bytes >= bytes) return PBRTGPU_OK;
     if (b.p) PG_CUDA(ctx, cudaFree(b.p));
@@ -75,6 +80,7 @@ int pbrtgpu_create(int cuda_device, pbrtgpu_ctx **out) {
     if (const char *v = getenv("PBRTGPU_TRACE_FUSED")) ctx->traceFused = atoi(v) != 0;
     if (const char *v = getenv("PBRTGPU_SHADE_SYNC")) ctx->shadeSync = atoi(v) != 0;
     if (const char *v = getenv("PBRTGPU_LIGHT_STAGE_BLOCKS")) ctx->lightStageBlocksPerSM = std::min(32, std::max(1, atoi(v)));
+    if (const char *v = getenv("PBRTGPU_LAYOUT")) ctx->layoutOnDevice = strcmp(v, "host") != 0;
     if (const char *v = getenv("PBRTGPU_SORT_HITS")) ctx->sortHits = atoi(v) != 0;
     if (const char *v = getenv("PBRTGPU_SHADE_LAMBERT")) ctx->shadeLambert = atoi(v) != 0;
     if (const char *v = getenv("PBRTGPU_LAMBERT_BLOCK")) ctx->lambertBlock = atoi(v);
@@ -112,6 +118,7 @@ void pbrtgpu_destroy(pbrtgpu_ctx *ctx) {
     for (auto &b : ctx->scratch)
         if (b.p) cudaFree(b.p);
     if (ctx->film.p) cudaFree(ctx->film.p);
+    if (ctx->layoutScratch.p) cudaFree(ctx->layoutScratch.p);
     if (ctx->dPerms) cudaFree(ctx->dPerms);
     if (ctx->dPrimes) cudaFree(ctx->dPrimes);
     if (ctx->dPrimeSums) cudaFree(ctx->dPrimeSums);
@@ -143,8 +150,10 @@ int pbrtgpu_upload_scene(pbrtgpu_ctx *ctx, const pbrtgpu_scene *s) {
     if (!s->bvh_bounds || !s->bvh_offset || !s->bvh_nprims || !s->bvh_axis || !s->prim_type || !s->tri_p || !s->prim_orig_id)
         return ctx->fail(PBRTGPU_ERR_INVALID, "scene arrays missing");
     // validate tree shape so that traversal cannot run away on bad input
+    int nInterior = 0;
     for (int i = 0; i < s->n_nodes; ++i) {
         if (s->bvh_nprims[i] == 0) {
+            ++nInterior;
             if (i + 1 >= s->n_nodes || s->bvh_offset[i] <= i || s->bvh_offset[i] >= s->n_nodes || s->bvh_axis[i] > 2)
                 return ctx->fail(PBRTGPU_ERR_INVALID, "BVH node %d: bad child offset / axis", i);
         } else if (s->bvh_offset[i] < 0 || s->bvh_offset[i] + (int)s->bvh_nprims[i] > s->n_prims)
@@ -154,22 +163,34 @@ int pbrtgpu_upload_scene(pbrtgpu_ctx *ctx, const pbrtgpu_scene *s) {
     DevScene &d = ctx->scene;
     memset(&d, 0, sizeof(d));
 
-    // the two layout conversions are independent: primitives on a second thread while this one does the nodes
-    std::vector<F4> wide, tris;
-    {
+    int rc;
+#define UP(host, count, dev) \
+    if ((rc = uploadArray(ctx, host, (size_t)(count), dev)) != PBRTGPU_OK) return rc;
+    UP(s->prim_flags, s->prim_flags ? s->n_prims : 0, &d.primFlags);
+    UP(s->tri_uv, s->tri_uv ? 6 * (size_t)s->n_prims : 0, &d.triUV);
+    int firstBadPrim = 0x7fffffff;
+    ctx->nWideRecords = 1 + nInterior;
+    if (ctx->layoutOnDevice) {
+        // the raw arrays go up as they are and kernels write the records (layout_device.cu)
+        void *nodes = nullptr, *tris = nullptr;
+        if ((rc = allocSceneArray(ctx, 64 * (size_t)(1 + nInterior), &nodes)) != PBRTGPU_OK) return rc;
+        if ((rc = allocSceneArray(ctx, 48 * (size_t)s->n_prims, &tris)) != PBRTGPU_OK) return rc;
+        if ((rc = buildLayoutOnDevice(ctx, s, nInterior, d.triUV, d.primFlags, (F4 *)nodes, (F4 *)tris, &firstBadPrim)) != PBRTGPU_OK) return rc;
+        d.bvh.nodes = (const F4 *)nodes;
+        d.bvh.tris = (const F4 *)tris;
+    } else {
+        // host conversion (layout_build.h): primitives on a second thread while this one does the nodes
+        std::vector<F4> wide, tris;
         std::string err;
         bool trisOk = true;
         std::thread trisThread([&] { trisOk = buildTris(s, &tris, &err); });
         buildWideNodes(s, &wide);
         trisThread.join();
         if (!trisOk) return ctx->fail(PBRTGPU_ERR_INVALID, "%s", err.c_str());
+        UP(wide.data(), wide.size(), &d.bvh.nodes);
+        UP(tris.data(), tris.size(), &d.bvh.tris);
+        PG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // the staging vectors go out of scope
     }
-
-    int rc;
-#define UP(host, count, dev) \
-    if ((rc = uploadArray(ctx, host, (size_t)(count), dev)) != PBRTGPU_OK) return rc;
-    UP(wide.data(), wide.size(), &d.bvh.nodes);
-    UP(tris.data(), tris.size(), &d.bvh.tris);
     UP(s->plane_params, (size_t)s->n_planes * PBRTGPU_PLANE_STRIDE, &d.bvh.planeParams);
     UP(s->sphere_params, (size_t)s->n_spheres * PBRTGPU_SPHERE_STRIDE, &d.bvh.sphereParams);
     d.nPrims = s->n_prims;
@@ -178,9 +199,7 @@ int pbrtgpu_upload_scene(pbrtgpu_ctx *ctx, const pbrtgpu_scene *s) {
     UP(s->prim_orig_id, s->n_prims, &d.primOrigId);
     UP(s->prim_material, s->prim_material ? s->n_prims : 0, &d.primMaterial);
     UP(s->prim_light, s->prim_light ? s->n_prims : 0, &d.primLight);
-    UP(s->prim_flags, s->prim_flags ? s->n_prims : 0, &d.primFlags);
     UP(s->tri_n, s->tri_n ? 9 * (size_t)s->n_prims : 0, &d.triN);
-    UP(s->tri_uv, s->tri_uv ? 6 * (size_t)s->n_prims : 0, &d.triUV);
     UP(s->tri_s, s->tri_s ? 9 * (size_t)s->n_prims : 0, &d.triS);
     UP(s->mat_tag, s->n_materials, &d.matTag);
     UP(s->mat_params, (size_t)s->n_materials * PBRTGPU_MAT_STRIDE, &d.matParams);
@@ -240,7 +259,21 @@ int pbrtgpu_upload_scene(pbrtgpu_ctx *ctx, const pbrtgpu_scene *s) {
     d.worldRadius = s->world_radius;
     PG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     drainScenePool(ctx);
+    if (firstBadPrim != 0x7fffffff) return ctx->fail(PBRTGPU_ERR_INVALID, "primitive %d: shape index out of range", firstBadPrim);
     ctx->haveScene = true;
+    return PBRTGPU_OK;
+}
+
+// Unit-parity hook: the device layout of the uploaded scene (bvh.h), for the byte-for-byte test of the device-side
+// conversion against layout_build.h.  nodes: 16 floats per record, tris: 12 floats per primitive slot.
+int pbrtgpu_debug_read_layout(pbrtgpu_ctx *ctx, float *nodes, int64_t n_records, float *tris, int64_t n_prims) {
+    if (!ctx) return PBRTGPU_ERR_INVALID;
+    if (!ctx->haveScene) return ctx->fail(PBRTGPU_ERR_STATE, "no scene uploaded");
+    if (n_records != ctx->nWideRecords || n_prims != ctx->scene.nPrims)
+        return ctx->fail(PBRTGPU_ERR_INVALID, "the uploaded scene has %lld records and %d primitives", ctx->nWideRecords, ctx->scene.nPrims);
+    PG_CUDA(ctx, cudaSetDevice(ctx->device));
+    PG_CUDA(ctx, cudaMemcpy(nodes, ctx->scene.bvh.nodes, 64 * (size_t)n_records, cudaMemcpyDeviceToHost));
+    PG_CUDA(ctx, cudaMemcpy(tris, ctx->scene.bvh.tris, 48 * (size_t)n_prims, cudaMemcpyDeviceToHost));
     return PBRTGPU_OK;
 }
 

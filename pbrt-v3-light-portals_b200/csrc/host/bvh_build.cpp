@@ -9,6 +9,7 @@
 #include <algorithm>
 #include <cstdio>
 
+#include "../common/upper_sah.h"
 #include "scene.h"
 
 namespace pg {
@@ -199,60 +200,31 @@ struct HLBuilder {
         return nodeIdx;
     }
 
-    int buildUpperSAH(std::vector<int> &roots, int start, int end) {
-        int nNodes = end - start;
-        if (nNodes == 1) return roots[start];
-        Bounds3 bounds;
-        for (int i = start; i < end; ++i) bounds = unionB(bounds, nodes[roots[i]].bounds);
-        Bounds3 centroidBounds;
-        for (int i = start; i < end; ++i) {
-            const Bounds3 &b = nodes[roots[i]].bounds;
-            centroidBounds = unionB(centroidBounds, (b.pMin + b.pMax) * 0.5f);
+    // buildUpperSAH (bvh.cpp:539-638) lives in common/upper_sah.h, shared with the device builder
+    int buildUpper(const std::vector<int> &treeletRoots) {
+        std::vector<UBox> rb(treeletRoots.size());
+        for (size_t t = 0; t < treeletRoots.size(); ++t) {
+            const Bounds3 &b = nodes[treeletRoots[t]].bounds;
+            rb[t].mn[0] = b.pMin.x, rb[t].mn[1] = b.pMin.y, rb[t].mn[2] = b.pMin.z;
+            rb[t].mx[0] = b.pMax.x, rb[t].mx[1] = b.pMax.y, rb[t].mx[2] = b.pMax.z;
         }
-        int dim = centroidBounds.maximumExtent();
-        // the reference CHECKs centroidBounds.pMax[dim] != pMin[dim] here and aborts otherwise (bvh.cpp:562)
-        constexpr int nBuckets = 12;
-        struct Bucket {
-            int count = 0;
-            Bounds3 bounds;
-        } buckets[nBuckets];
-        const float cMin = centroidBounds.pMin[dim], cMax = centroidBounds.pMax[dim];
-        auto bucketOf = [&](int root) {
-            const Bounds3 &b = nodes[root].bounds;
-            float centroid = (b.pMin[dim] + b.pMax[dim]) * 0.5f;
-            int k = (int)(nBuckets * ((centroid - cMin) / (cMax - cMin)));
-            if (k == nBuckets) k = nBuckets - 1;
-            return k;
-        };
-        for (int i = start; i < end; ++i) {
-            int k = bucketOf(roots[i]);
-            buckets[k].count++;
-            buckets[k].bounds = unionB(buckets[k].bounds, nodes[roots[i]].bounds);
+        UpperSAH up;
+        up.rootBounds = &rb;
+        std::vector<int> order(treeletRoots.size());
+        for (size_t t = 0; t < order.size(); ++t) order[t] = (int)t;
+        int rootRef = up.build(order, 0, (int)order.size());
+        int base = (int)nodes.size();
+        auto nodeOf = [&](int ref) { return ref >= 0 ? base + ref : treeletRoots[~ref]; };
+        for (const UpperNode &u : up.nodes) {
+            BuildNode n;
+            n.bounds.pMin = v3(u.bounds.mn[0], u.bounds.mn[1], u.bounds.mn[2]);
+            n.bounds.pMax = v3(u.bounds.mx[0], u.bounds.mx[1], u.bounds.mx[2]);
+            n.child[0] = nodeOf(u.child[0]), n.child[1] = nodeOf(u.child[1]);
+            n.splitAxis = u.axis;
+            n.nPrimitives = 0;
+            nodes.push_back(n);
         }
-        float cost[nBuckets - 1];
-        for (int i = 0; i < nBuckets - 1; ++i) {
-            Bounds3 b0, b1;
-            int count0 = 0, count1 = 0;
-            for (int j = 0; j <= i; ++j) b0 = unionB(b0, buckets[j].bounds), count0 += buckets[j].count;
-            for (int j = i + 1; j < nBuckets; ++j) b1 = unionB(b1, buckets[j].bounds), count1 += buckets[j].count;
-            cost[i] = .125f + (count0 * b0.surfaceArea() + count1 * b1.surfaceArea()) / bounds.surfaceArea();
-        }
-        float minCost = cost[0];
-        int minCostSplitBucket = 0;
-        for (int i = 1; i < nBuckets - 1; ++i)
-            if (cost[i] < minCost) minCost = cost[i], minCostSplitBucket = i;
-        int *pmid = std::partition(&roots[start], &roots[end - 1] + 1, [&](int root) { return bucketOf(root) <= minCostSplitBucket; });
-        int mid = (int)(pmid - &roots[0]);
-        int nodeIdx = (int)nodes.size();
-        nodes.emplace_back();
-        int c0 = buildUpperSAH(roots, start, mid);
-        int c1 = buildUpperSAH(roots, mid, end);
-        BuildNode &n = nodes[nodeIdx];
-        n.child[0] = c0, n.child[1] = c1;
-        n.bounds = unionB(nodes[c0].bounds, nodes[c1].bounds);
-        n.splitAxis = dim;
-        n.nPrimitives = 0;
-        return nodeIdx;
+        return nodeOf(rootRef);
     }
 
     int build() {
@@ -274,7 +246,7 @@ struct HLBuilder {
                 roots.push_back(emitLBVH(&mp[start], end - start, 29 - 12));
                 start = end;
             }
-        return buildUpperSAH(roots, 0, (int)roots.size());
+        return buildUpper(roots);
     }
 };
 

@@ -78,6 +78,9 @@ int pbrthost_write_image(const pbrthost_scene *s, const char *filename, const fl
                : PBRTGPU_ERR_INVALID;
 }
 
+void pbrthost_set_hlbvh_builder(pbrthost_hlbvh_builder fn, void *user) { pg::setHlbvhBuilder(fn, user); }
+void pbrthost_last_bvh_build_ms(double *wall_ms, float *builder_ms) { pg::lastBvhBuildMs(wall_ms, builder_ms); }
+
 int pbrthost_halton_permutations(uint16_t *out, int64_t n) {
     std::vector<uint16_t> perms = pg::radicalInversePermutations(pg::firstPrimes());
     if (!out || n != (int64_t)perms.size()) return PBRTGPU_ERR_INVALID;

@@ -3,6 +3,7 @@
 // camera/film/sampler/integrator parameters into pbrtgpu_render_params
 // (RenderOptions::MakeIntegrator/MakeCamera, api.cpp:1774-1847).
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <functional>
 #include <cstring>
@@ -53,6 +54,18 @@ pbrtgpu_scene FlatScene::view() const {
     return s;
 }
 
+namespace {
+pbrthost_hlbvh_builder gHlbvhBuilder = nullptr;
+void *gHlbvhUser = nullptr;
+double gBuildWallMs = 0;
+float gBuilderMs = 0;
+}  // namespace
+void setHlbvhBuilder(pbrthost_hlbvh_builder fn, void *user) { gHlbvhBuilder = fn, gHlbvhUser = user; }
+void lastBvhBuildMs(double *wallMs, float *builderMs) {
+    if (wallMs) *wallMs = gBuildWallMs;
+    if (builderMs) *builderMs = gBuilderMs;
+}
+
 bool flattenScene(const SceneDesc &desc, FlatScene *out, std::string *err) {
     FlatScene &fs = *out;
     // MakeAccelerator("bvh"), accelerators/bvh.cpp:740-760
@@ -75,7 +88,25 @@ bool flattenScene(const SceneDesc &desc, FlatScene *out, std::string *err) {
     size_t n = desc.prims.size();
     std::vector<Bounds3> pb(n);
     for (size_t i = 0; i < n; ++i) pb[i] = primWorldBound(desc, desc.prims[i]);
-    BuiltBVH bvh = buildBVH(pb, maxPrimsInNode, sm);
+    BuiltBVH bvh;
+    auto t0 = std::chrono::steady_clock::now();
+    gBuilderMs = 0;
+    if (sm == SplitMethod::HLBVH && gHlbvhBuilder && n > 0) {
+        // the treelets are built by the installed builder (libpbrtgpu's pbrtgpu_build_hlbvh); same tree, node for node
+        static_assert(sizeof(Bounds3) == 6 * sizeof(float), "Bounds3 is six floats");
+        size_t cap = 2 * n;
+        bvh.bounds.resize(6 * cap), bvh.offset.resize(cap), bvh.nPrims.resize(cap), bvh.axis.resize(cap), bvh.orderedPrims.resize(n);
+        int32_t nNodes = 0;
+        int rc = gHlbvhBuilder(gHlbvhUser, &pb[0].pMin.x, (int32_t)n, maxPrimsInNode, (int32_t)cap, bvh.bounds.data(), bvh.offset.data(),
+                               bvh.nPrims.data(), bvh.axis.data(), bvh.orderedPrims.data(), &nNodes, &gBuilderMs);
+        if (rc != 0 || nNodes <= 0) {
+            if (err) *err = "the installed HLBVH builder failed (status " + std::to_string(rc) + ")";
+            return false;
+        }
+        bvh.bounds.resize(6 * (size_t)nNodes), bvh.offset.resize(nNodes), bvh.nPrims.resize(nNodes), bvh.axis.resize(nNodes);
+    } else
+        bvh = buildBVH(pb, maxPrimsInNode, sm);
+    gBuildWallMs = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
     fs.bvhBounds = std::move(bvh.bounds);
     fs.bvhOffset = std::move(bvh.offset);
     fs.bvhNPrims = std::move(bvh.nPrims);

@@ -15,7 +15,7 @@ import numpy as np
 import pytest
 
 import util
-from conftest import GOLDEN, scene_path
+from conftest import GOLDEN, ROOT, scene_path
 
 SCENE = "tri_soup.pbrt"
 
@@ -220,3 +220,114 @@ def test_sphere_early_out_never_rejects_a_hit(pkg, hostsim_lib):
         total_rej += int(rej.sum())
         total += int((acc == 0).sum())
     assert total_rej > 0.5 * total  # and it is worth having: it catches most of the rays the full test rejects
+
+
+# ---------------------------------------------------------------- HLBVH built on the device
+def _scene_arrays(hs):
+    v = hs.view
+    out = {"bvh_bounds": util.bits(v.array("bvh_bounds", v.n_nodes, 6)).copy()}
+    for name, count in (("bvh_offset", v.n_nodes), ("bvh_nprims", v.n_nodes), ("bvh_axis", v.n_nodes), ("prim_orig_id", v.n_prims),
+                        ("prim_type", v.n_prims), ("prim_material", v.n_prims), ("prim_light", v.n_prims)):
+        out[name] = np.array(v.array(name, count))
+    out["tri_p"] = util.bits(v.array("tri_p", v.n_prims, 9)).copy()
+    return out
+
+
+def _load_both_ways(pkg, gpu, text, base_dir):
+    """The same scene text with the host's HLBVHBuild and with pbrtgpu_build_hlbvh installed as pbrthost's builder."""
+    host = pkg.HostScene(text=text, base_dir=base_dir)
+    gpu.install_hlbvh_builder(True)
+    try:
+        dev = pkg.HostScene(text=text, base_dir=base_dir)
+        wall_ms, dev_ms = pkg.last_bvh_build_ms()
+    finally:
+        gpu.install_hlbvh_builder(False)
+    assert dev_ms > 0, "the device builder was not called"
+    return host, dev
+
+
+def _random_triangles_scene(n, seed, extra="", maxnodeprims=4, clumps=0):
+    """n small random triangles in a 10^3 box; `clumps` > 0 puts every triangle's centroid on one of that many points, so that
+    whole groups share a Morton code (emitLBVH's bitIndex == -1 leaves, bvh.cpp:481)."""
+    rng = np.random.default_rng(seed)
+    if clumps:
+        c = rng.uniform(-5, 5, (clumps, 3))[rng.integers(0, clumps, n)]
+        d = rng.normal(0, 0.05, (n, 2, 3))
+        tri = np.stack([c + d[:, 0], c + d[:, 1], c - d[:, 0] - d[:, 1]], 1)  # centroid of the bounds is not c exactly, but within a cell
+    else:
+        c = rng.uniform(-5, 5, (n, 1, 3))
+        tri = c + rng.normal(0, 0.05, (n, 3, 3))
+    P = " ".join("%.9g" % x for x in tri.astype(np.float32).ravel())
+    idx = " ".join(str(i) for i in range(3 * n))
+    return ('LookAt 0 -20 0  0 0 0  0 0 1\nCamera "perspective" "float fov" [40]\n'
+            'Film "image" "integer xresolution" [16] "integer yresolution" [16] "string filename" "t.pfm"\n'
+            'Sampler "halton" "integer pixelsamples" [1]\nIntegrator "path"\n'
+            'Accelerator "bvh" "string splitmethod" "hlbvh" "integer maxnodeprims" [%d]\nWorldBegin\n%s'
+            'LightSource "point" "point from" [0 -15 5]\nMaterial "matte"\n'
+            'Shape "trianglemesh" "integer indices" [%s] "point P" [%s]\nWorldEnd\n' % (maxnodeprims, extra, idx, P))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", ["one", "three", "soup", "random_60k", "random_60k_leaf1", "random_60k_leaf255", "clumps", "killeroo"])
+def test_gpu_hlbvh_build_matches_host_build(pkg, gpu, case):
+    """pbrtgpu_build_hlbvh (device/bvh_build.cu) against the host's HLBVHBuild, which is pinned node for node to the
+    reference's (test_host_bvh_split_methods_match_live_reference): the LinearBVHNode array bit for bit, the primitive order,
+    and everything flattened in that order.  From one primitive to 133 000, maxnodeprims 1 / 4 / 255, shared Morton codes."""
+    base = os.path.join(ROOT, "tests", "scenes")
+    if case == "soup":
+        text = open(scene_path("tri_soup.pbrt")).read().replace("WorldBegin", 'Accelerator "bvh" "string splitmethod" "hlbvh"\nWorldBegin', 1)
+    elif case == "killeroo":
+        p = scene_path("killeroo-path.pbrt")
+        base = os.path.dirname(p)
+        text = open(p).read().replace("WorldBegin", 'Accelerator "bvh" "string splitmethod" "hlbvh"\nWorldBegin', 1)
+    elif case == "one":
+        text = _random_triangles_scene(1, 1)
+    elif case == "three":
+        text = _random_triangles_scene(3, 2)
+    elif case == "clumps":
+        text = _random_triangles_scene(20000, 3, clumps=37)
+    else:
+        text = _random_triangles_scene(60000, 4, maxnodeprims={"random_60k": 4, "random_60k_leaf1": 1, "random_60k_leaf255": 255}[case])
+    host, dev = _load_both_ways(pkg, gpu, text, base)
+    a, b = _scene_arrays(host), _scene_arrays(dev)
+    assert host.view.n_nodes == dev.view.n_nodes and host.view.n_prims == dev.view.n_prims
+    for k in a:
+        assert np.array_equal(a[k], b[k]), k
+    if case == "clumps":
+        assert a["bvh_nprims"].max() > 4  # leaves made because the Morton bits ran out, not because the range was small
+
+
+@pytest.mark.gpu
+def test_gpu_hlbvh_tree_traces_like_the_reference(pkg, gpu, ref_harness, tmp_path):
+    """End to end: a scene whose tree was built on the GPU, traced on the GPU, against the reference's own BVHAccel
+    (splitmethod hlbvh) on the same rays: hit IDs and t bit for bit."""
+    import subprocess
+    if not ref_harness:
+        pytest.skip("oracle/_ref not built")
+    text = _random_triangles_scene(60000, 9)
+    path = str(tmp_path / "s.pbrt")
+    open(path, "w").write(text)
+    _, dev = _load_both_ways(pkg, gpu, text, str(tmp_path))
+    rays = np.concatenate([util.rays_incoherent_closest(dev.view, 200000, seed=3), util.rays_toward_box(100000, [-6, -6, -6], [6, 6, 6], seed=4)])
+    rays.tofile(str(tmp_path / "r.bin"))
+    subprocess.check_call([ref_harness, "intersect", path, str(tmp_path / "r.bin"), str(tmp_path / "o.bin"), "closest", str(os.cpu_count() or 1)],
+                          stdout=subprocess.DEVNULL)
+    ref = np.fromfile(str(tmp_path / "o.bin"), dtype=[("id", "<i4"), ("t", "<f4")])
+    gpu.upload(dev)
+    ids, t, _ = gpu.intersect_closest(rays)
+    assert np.array_equal(ids, ref["id"]) and np.array_equal(util.bits(t), util.bits(ref["t"]))
+    assert (ids >= 0).sum() > 10000
+
+
+@pytest.mark.gpu
+def test_gpu_hlbvh_build_rejects_bad_arguments(pkg, gpu):
+    import ctypes as C
+    lib = pkg.gpu_lib()
+    pb = np.zeros((4, 6), np.float32)
+    out = np.zeros(64, np.float32)
+    m = C.c_int32(0)
+    rc = lib.pbrtgpu_build_hlbvh(gpu._h, pb.ctypes.data, 4, 4, 7, out.ctypes.data, out.ctypes.data, out.ctypes.data, out.ctypes.data, out.ctypes.data,
+                                 C.byref(m), None)
+    assert rc == -3 and b"node_capacity" in lib.pbrtgpu_last_error(gpu._h)
+    assert lib.pbrtgpu_build_hlbvh(gpu._h, None, 4, 4, 8, out.ctypes.data, out.ctypes.data, out.ctypes.data, out.ctypes.data, out.ctypes.data,
+                                   C.byref(m), None) == -3

@@ -149,7 +149,7 @@ int pbrtgpu_upload_scene(pbrtgpu_ctx *ctx, const pbrtgpu_scene *s) {
     if (s->n_nodes <= 0 || s->n_prims <= 0) return ctx->fail(PBRTGPU_ERR_INVALID, "scene has no primitives");
     if (!s->bvh_bounds || !s->bvh_offset || !s->bvh_nprims || !s->bvh_axis || !s->prim_type || !s->tri_p || !s->prim_orig_id)
         return ctx->fail(PBRTGPU_ERR_INVALID, "scene arrays missing");
-    // validate tree shape so that traversal cannot run away on bad input
+    // validate the tree shape, so that traversal cannot run away on bad input ...
     int nInterior = 0;
     for (int i = 0; i < s->n_nodes; ++i) {
         if (s->bvh_nprims[i] == 0) {
@@ -158,6 +158,38 @@ int pbrtgpu_upload_scene(pbrtgpu_ctx *ctx, const pbrtgpu_scene *s) {
                 return ctx->fail(PBRTGPU_ERR_INVALID, "BVH node %d: bad child offset / axis", i);
         } else if (s->bvh_offset[i] < 0 || s->bvh_offset[i] + (int)s->bvh_nprims[i] > s->n_prims)
             return ctx->fail(PBRTGPU_ERR_INVALID, "BVH leaf %d: primitive range out of bounds", i);
+    }
+    // ... and every index the kernels use to address a table, so that a bad caller gets PBRTGPU_ERR_INVALID, not a device fault
+    if ((s->n_materials > 0 && (!s->mat_tag || !s->mat_params)) || (s->n_lights > 0 && (!s->light_tag || !s->light_params || !s->light_prim)))
+        return ctx->fail(PBRTGPU_ERR_INVALID, "material / light tables missing");
+    for (int i = 0; i < s->n_materials; ++i)
+        if (s->mat_tag[i] < PBRTGPU_MAT_NONE || s->mat_tag[i] > PBRTGPU_MAT_UBER) return ctx->fail(PBRTGPU_ERR_INVALID, "material %d: unknown tag %d", i, s->mat_tag[i]);
+    for (int i = 0; i < s->n_prims; ++i) {
+        if (s->prim_type[i] > PBRTGPU_PRIM_SPHERE) return ctx->fail(PBRTGPU_ERR_INVALID, "primitive %d: unknown type %d", i, (int)s->prim_type[i]);
+        if (s->prim_material && (s->prim_material[i] < -1 || s->prim_material[i] >= s->n_materials))
+            return ctx->fail(PBRTGPU_ERR_INVALID, "primitive %d: material index %d out of range", i, s->prim_material[i]);
+        if (s->prim_light && (s->prim_light[i] < -1 || s->prim_light[i] >= s->n_lights))
+            return ctx->fail(PBRTGPU_ERR_INVALID, "primitive %d: light index %d out of range", i, s->prim_light[i]);
+    }
+    for (int i = 0; i < s->n_lights; ++i) {
+        const int tag = s->light_tag[i];
+        if (tag < PBRTGPU_LIGHT_DIFFUSE_AREA || tag > PBRTGPU_LIGHT_SPOT) return ctx->fail(PBRTGPU_ERR_INVALID, "light %d: unknown tag %d", i, tag);
+        const bool area = tag == PBRTGPU_LIGHT_DIFFUSE_AREA || tag == PBRTGPU_LIGHT_PORTAL_AREA;
+        if (area && (s->light_prim[i] < 0 || s->light_prim[i] >= s->n_prims))
+            return ctx->fail(PBRTGPU_ERR_INVALID, "light %d: area light without a valid primitive (%d)", i, s->light_prim[i]);
+        if (tag == PBRTGPU_LIGHT_PORTAL_AREA) {
+            if (s->prim_type[s->light_prim[i]] != PBRTGPU_PRIM_AAPLANE) return ctx->fail(PBRTGPU_ERR_INVALID, "light %d: a portal light's shape must be an aaplane", i);
+            if (!s->light_strategy || s->light_strategy[i] < PBRTGPU_PORTAL_UNIFORM_PORTAL || s->light_strategy[i] > PBRTGPU_PORTAL_SOLIDANGLE_MIS3)
+                return ctx->fail(PBRTGPU_ERR_INVALID, "light %d: unknown portal strategy", i);
+            if (!s->light_portal_begin) return ctx->fail(PBRTGPU_ERR_INVALID, "light %d: light_portal_begin missing", i);
+        }
+    }
+    if (s->light_portal_begin) {
+        if (s->n_portals > 0 && !s->portal_params) return ctx->fail(PBRTGPU_ERR_INVALID, "portal_params missing");
+        if (s->n_lights > 0 && s->light_portal_begin[0] < 0) return ctx->fail(PBRTGPU_ERR_INVALID, "light_portal_begin must start at 0 or above");
+        for (int i = 0; i < s->n_lights; ++i)
+            if (s->light_portal_begin[i + 1] < s->light_portal_begin[i] || s->light_portal_begin[i + 1] > s->n_portals)
+                return ctx->fail(PBRTGPU_ERR_INVALID, "light %d: portal range [%d, %d) not inside [0, %d)", i, s->light_portal_begin[i], s->light_portal_begin[i + 1], s->n_portals);
     }
     freeScene(ctx, /*keepForReuse=*/true);
     DevScene &d = ctx->scene;

@@ -148,7 +148,18 @@ int SceneApi::makeMaterial(const std::string &name, const ParamSet &shapeParams,
         m.tag = PBRTGPU_MAT_MIRROR;
         put3(m.params + 0, mp.spectrum("Kr", RGB(0.9f)).clamp());
     } else {
-        if (name != "matte") hostWarning("Material \"%s\" is not supported by the GPU path integrator. Using \"matte\".", name.c_str());
+        if (name != "matte") {
+            // MakeMaterial (api.cpp:548-617): a name the reference does not know becomes matte with a warning, there and here.
+            // A material the reference DOES implement but this library does not is refused: rendering it as matte would be a
+            // silently different image.
+            for (const char *known : {"translucent", "hair", "disney", "mix", "substrate", "subsurface", "kdsubsurface", "fourier"})
+                if (name == known) {
+                    hostError("Material \"%s\" is not supported by the GPU path integrator", name.c_str());
+                    failed = true;
+                    return -1;
+                }
+            hostWarning("Material \"%s\" unknown. Using \"matte\".", name.c_str());
+        }
         m.tag = PBRTGPU_MAT_MATTE;  // materials/matte.cpp:45-73
         put3(m.params + 0, mp.spectrum("Kd", RGB(0.5f)).clamp());
         m.params[3] = clampf(mp.scalar("sigma", 0.f), 0, 90);

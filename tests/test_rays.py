@@ -246,7 +246,7 @@ def _load_both_ways(pkg, gpu, text, base_dir):
     return host, dev
 
 
-def _random_triangles_scene(n, seed, extra="", maxnodeprims=4, clumps=0):
+def _random_triangles_scene(n, seed, extra="", maxnodeprims=4, clumps=0, degenerate=0):
     """n small random triangles in a 10^3 box; `clumps` > 0 puts every triangle's centroid on one of that many points, so that
     whole groups share a Morton code (emitLBVH's bitIndex == -1 leaves, bvh.cpp:481)."""
     rng = np.random.default_rng(seed)
@@ -257,6 +257,7 @@ def _random_triangles_scene(n, seed, extra="", maxnodeprims=4, clumps=0):
     else:
         c = rng.uniform(-5, 5, (n, 1, 3))
         tri = c + rng.normal(0, 0.05, (n, 3, 3))
+    tri[:degenerate, 2] = tri[:degenerate, 1]  # zero-area triangles: Triangle::Intersect rejects them (triangle.cpp:309-317)
     P = " ".join("%.9g" % x for x in tri.astype(np.float32).ravel())
     idx = " ".join(str(i) for i in range(3 * n))
     return ('LookAt 0 -20 0  0 0 0  0 0 1\nCamera "perspective" "float fov" [40]\n'
@@ -331,3 +332,33 @@ def test_gpu_hlbvh_build_rejects_bad_arguments(pkg, gpu):
     assert rc == -3 and b"node_capacity" in lib.pbrtgpu_last_error(gpu._h)
     assert lib.pbrtgpu_build_hlbvh(gpu._h, None, 4, 4, 8, out.ctypes.data, out.ctypes.data, out.ctypes.data, out.ctypes.data, out.ctypes.data,
                                    C.byref(m), None) == -3
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", ["soup", "killeroo", "box_glass", "sphere_lights", "portal_room", "random_60k"])
+def test_gpu_layout_conversion_matches_host_restatement(pkg, gpu, case, monkeypatch):
+    """pbrtgpu_upload_scene builds the device layout (64-byte two-child records, 48-byte primitive slots with their tags:
+    type, degenerate, last-in-leaf, shape index) with kernels (device/layout_device.cu); PBRTGPU_LAYOUT=host builds it with the
+    CPU restatement the hostsim tests run on (device/layout_build.h).  Same bytes."""
+    base = os.path.join(ROOT, "tests", "scenes")
+    if case == "random_60k":
+        hs = pkg.HostScene(text=_random_triangles_scene(60000, 4, degenerate=70), base_dir=base)
+    elif case == "portal_room":
+        hs = pkg.HostScene(text=open(scene_path("portal_room.pbrt")).read().replace("STRATEGY", "portal"), base_dir=base)
+    else:
+        hs = pkg.HostScene(scene_path({"soup": "tri_soup.pbrt", "killeroo": "killeroo-path.pbrt", "box_glass": "box_glass.pbrt",
+                                       "sphere_lights": "sphere_lights.pbrt"}[case]))
+    gpu.upload(hs)
+    nodes_d, tris_d = gpu.read_layout(hs)
+    monkeypatch.setenv("PBRTGPU_LAYOUT", "host")
+    other = pkg.GpuContext(0)
+    try:
+        other.upload(hs)
+        nodes_h, tris_h = other.read_layout(hs)
+    finally:
+        other.close()
+    assert np.array_equal(nodes_d, nodes_h)
+    assert np.array_equal(tris_d, tris_h)
+    assert ((tris_d[:, 3] & 8) != 0).sum() == (np.asarray(hs.view.array("bvh_nprims", hs.view.n_nodes)) != 0).sum()  # one kTagLast per leaf
+    if case == "random_60k":
+        assert ((tris_d[:, 3] & 4) != 0).sum() == 70  # kTagDegenerate

@@ -128,6 +128,20 @@ def test_directlighting_refuses_what_the_tree_walk_cannot_reproduce(pkg):
         pkg.HostScene(text=text, base_dir=os.path.join(ROOT, "tests", "scenes"))
 
 
+def test_materials_the_reference_has_and_this_library_does_not_are_refused(pkg):
+    """MakeMaterial (api.cpp:548-617): a name the reference does not know becomes matte with a warning -- same here; a material the
+    reference implements and this library does not must fail the load instead of rendering as matte."""
+    text = open(scene_path("tri_soup.pbrt")).read()
+    assert 'Material "matte"' in text
+    for name in ("substrate", "translucent", "disney", "hair", "mix", "subsurface", "kdsubsurface", "fourier"):
+        with pytest.raises(pkg.PbrtGpuError):
+            pkg.HostScene(text=text.replace('Material "matte"', 'Material "%s"' % name), base_dir=os.path.join(ROOT, "tests", "scenes"))
+    a = pkg.HostScene(text=text.replace('Material "matte"', 'Material "no_such_material"'), base_dir=os.path.join(ROOT, "tests", "scenes"))
+    b = pkg.HostScene(text=text, base_dir=os.path.join(ROOT, "tests", "scenes"))
+    assert a.view.n_materials == b.view.n_materials
+    assert np.array_equal(np.asarray(a.view.array("mat_tag", a.view.n_materials)), np.asarray(b.view.array("mat_tag", b.view.n_materials)))
+
+
 def test_directlighting_tree_rounds_carry_pending_branches(pkg, hostsim_lib, golden, monkeypatch):
     """Paths that still hold pending transmission branches after a round of iterations continue in another round
     (render_host.inc, anotherRound; hostsim mirrors it): three iterations per round must give the same image."""
@@ -381,6 +395,29 @@ def test_gpu_render_errors(pkg, gpu):
     p.spp = 0
     with pytest.raises(pkg.PbrtGpuError):
         gpu.render(p)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("field,value", [("prim_material", 99), ("prim_material", -2), ("prim_light", 7), ("light_prim", 10 ** 6),
+                                         ("light_portal_begin", 50), ("light_strategy", 17), ("mat_tag", 40), ("light_tag", 0)])
+def test_gpu_upload_refuses_indices_outside_their_tables(pkg, gpu, field, value):
+    """Every index the kernels address a table with is range-checked by pbrtgpu_upload_scene: a bad caller gets
+    PBRTGPU_ERR_INVALID and a message, not an out-of-bounds device read."""
+    import ctypes as C
+    hs = pkg.HostScene(text=open(scene_path("portal_room.pbrt")).read().replace("STRATEGY", "portal"), base_dir=os.path.join(ROOT, "tests", "scenes"))
+    v = type(hs.view)()
+    C.memmove(C.addressof(v), C.addressof(hs.view), C.sizeof(v))
+    count = {"prim_material": v.n_prims, "prim_light": v.n_prims, "light_prim": v.n_lights, "light_portal_begin": v.n_lights + 1,
+             "light_strategy": v.n_lights, "mat_tag": v.n_materials, "light_tag": v.n_lights}[field]
+    bad = np.array(hs.view.array(field, count)).copy()
+    bad[-1] = value
+    setattr(v, field, bad.ctypes.data_as(C.POINTER(C.c_int32)))
+    rc = pkg.gpu_lib().pbrtgpu_upload_scene(gpu._h, C.byref(v))
+    assert rc == -3, (field, rc)
+    assert len(pkg.gpu_lib().pbrtgpu_last_error(gpu._h)) > 10
+    gpu.upload(hs)  # the context is still usable
+    film, _ = gpu.render(hs.params)
+    assert np.isfinite(film).all()
 
 
 @pytest.mark.gpu

@@ -150,6 +150,13 @@ PG_HD int maxDimension(V3 v) {
     return (v.x > v.y) ? ((v.x > v.z) ? 0 : 2) : ((v.y > v.z) ? 1 : 2);
 }
 PG_HD V3 permute(V3 v, int x, int y, int z) { return v3(v[x], v[y], v[z]); }
+// permute(v, kx, ky, kz) for the triples Triangle::Intersect uses (kz = the ray's largest direction component, kx = kz + 1,
+// ky = kx + 1, both modulo 3; triangle.cpp:205-210): a rotation of the components, so two predicates select it
+// (six conditional moves) where the indexed form compiles to a chain of branches per component.
+PG_HD V3 rotateToZ(V3 v, int kz) {
+    const bool z0 = kz == 0, z1 = kz == 1;
+    return v3(z0 ? v.y : (z1 ? v.z : v.x), z0 ? v.z : (z1 ? v.x : v.y), z0 ? v.x : (z1 ? v.y : v.z));
+}
 PG_HD V3 faceforward(V3 n, V3 v) { return (dot(n, v) < 0.f) ? -n : n; }
 // geometry.h:1173-1180
 PG_HD void coordinateSystem(V3 v1, V3 *v2, V3 *v3o) {

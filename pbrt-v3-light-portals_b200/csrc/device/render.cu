@@ -99,17 +99,16 @@ struct FusedQueue {
     const F4 *path, *nee, *shadow;
     int nPath, nNee;
     __device__ __forceinline__ int operator()(int idx, Ray *ray) const {
-        if (idx < nPath) {
-            *ray = loadRayF4(path, idx);
-            return 0;
+        // one load site: the sub-queue only selects the address (three load sites made the compiler keep the ray in local memory)
+        const F4 *q = path;
+        int kind = 0;
+        if (idx >= nPath) {
+            idx -= nPath;
+            q = nee, kind = 2;
+            if (idx >= nNee) idx -= nNee, q = shadow, kind = 1;
         }
-        idx -= nPath;
-        if (idx < nNee) {
-            *ray = loadRayF4(nee, idx);
-            return 2;
-        }
-        *ray = loadRayF4(shadow, idx - nNee);
-        return 1;
+        *ray = loadRayF4(q, idx);
+        return kind;
     }
 };
 

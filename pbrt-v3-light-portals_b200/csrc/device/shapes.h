@@ -27,7 +27,7 @@ PG_HD RayShear rayShear(V3 rd) {
     if (s.kx == 3) s.kx = 0;
     s.ky = s.kx + 1;
     if (s.ky == 3) s.ky = 0;
-    V3 d = permute(rd, s.kx, s.ky, s.kz);
+    V3 d = rotateToZ(rd, s.kz);
     s.Sx = -d.x / d.z, s.Sy = -d.y / d.z, s.Sz = 1.f / d.z;
     return s;
 }
@@ -38,9 +38,9 @@ PG_HD RayShear rayShear(V3 rd) {
 PG_HD bool triangleTestSheared(const Ray &ray, const RayShear &sh, V3 p0, V3 p1, V3 p2, float *tOut, float *b0Out, float *b1Out,
                                float *b2Out = nullptr) {
     V3 p0t = p0 - ray.o, p1t = p1 - ray.o, p2t = p2 - ray.o;
-    p0t = permute(p0t, sh.kx, sh.ky, sh.kz);
-    p1t = permute(p1t, sh.kx, sh.ky, sh.kz);
-    p2t = permute(p2t, sh.kx, sh.ky, sh.kz);
+    p0t = rotateToZ(p0t, sh.kz);  // = permute(p, kx, ky, kz)
+    p1t = rotateToZ(p1t, sh.kz);
+    p2t = rotateToZ(p2t, sh.kz);
     float Sx = sh.Sx, Sy = sh.Sy, Sz = sh.Sz;
     p0t.x += Sx * p0t.z;
     p0t.y += Sy * p0t.z;

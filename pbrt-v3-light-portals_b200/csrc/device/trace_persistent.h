@@ -33,14 +33,16 @@ __device__ __forceinline__ Ray loadRayF4(const F4 *__restrict__ rays, int i) {
 
 // slabPartial (bvh.h) without the early returns: the same comparisons and the same
 // conditional updates, combined at the end (values computed past a failed test are unused).
-__device__ __forceinline__ bool slabPartialFlat(V3 bmin, V3 bmax, V3 o, V3 invDir, const bool dirIsNeg[3], float *tMinOut) {
+// The three dirIsNeg flags come as values (the traversal derives them from invDir's signs each round: three compares
+// instead of three bytes of per-ray state that the 64-register budget keeps in local memory).
+__device__ __forceinline__ bool slabPartialFlat(V3 bmin, V3 bmax, V3 o, V3 invDir, bool negX, bool negY, bool negZ, float *tMinOut) {
     const float k = 1 + 2 * gammaf(3);
-    float tMin = ((dirIsNeg[0] ? bmax.x : bmin.x) - o.x) * invDir.x;
-    float tMax = ((dirIsNeg[0] ? bmin.x : bmax.x) - o.x) * invDir.x;
-    float tyMin = ((dirIsNeg[1] ? bmax.y : bmin.y) - o.y) * invDir.y;
-    float tyMax = ((dirIsNeg[1] ? bmin.y : bmax.y) - o.y) * invDir.y;
-    float tzMin = ((dirIsNeg[2] ? bmax.z : bmin.z) - o.z) * invDir.z;
-    float tzMax = ((dirIsNeg[2] ? bmin.z : bmax.z) - o.z) * invDir.z;
+    float tMin = ((negX ? bmax.x : bmin.x) - o.x) * invDir.x;
+    float tMax = ((negX ? bmin.x : bmax.x) - o.x) * invDir.x;
+    float tyMin = ((negY ? bmax.y : bmin.y) - o.y) * invDir.y;
+    float tyMax = ((negY ? bmin.y : bmax.y) - o.y) * invDir.y;
+    float tzMin = ((negZ ? bmax.z : bmin.z) - o.z) * invDir.z;
+    float tzMax = ((negZ ? bmin.z : bmax.z) - o.z) * invDir.z;
     tMax *= k;
     tyMax *= k;
     tzMax *= k;
@@ -88,7 +90,6 @@ __device__ __forceinline__ void tracePersistent(const DevBVH &bvh, Source source
     ray.o = ray.d = v3(0.f);
     ray.tMax = 0;
     V3 invDir = v3(0.f);
-    bool dirIsNeg[3] = {false, false, false};
     int topRef = 0;    // the top stack entry lives in registers: a pop does not wait for local memory
     float topT = 0;
     RayShear shear = {0, 1, 2, 0.f, 0.f, 0.f};
@@ -125,7 +126,6 @@ __device__ __forceinline__ void tracePersistent(const DevBVH &bvh, Source source
                         idx = mine;
                         kind = source(idx, &ray);
                         invDir = v3(1 / ray.d.x, 1 / ray.d.y, 1 / ray.d.z);
-                        dirIsNeg[0] = invDir.x < 0, dirIsNeg[1] = invDir.y < 0, dirIsNeg[2] = invDir.z < 0;
                         shear = rayShear(ray.d);
                         hit.prim = -1;
                         sp = 0;
@@ -147,10 +147,15 @@ __device__ __forceinline__ void tracePersistent(const DevBVH &bvh, Source source
                 F4 q0 = __ldg(nd), q1 = __ldg(nd + 1), q2 = __ldg(nd + 2), q3 = __ldg(nd + 3);
                 if (COUNT) cnt[MODE == kTraceMixed ? kind : 0].nodes += 2;
                 int ref0 = f2i(q3.x), ref1 = f2i(q3.y), axis = f2i(q3.z);
-                float t0, t1;
-                bool ok0 = ref0 != kEmptyRef && slabPartialFlat(v3(q0.x, q0.y, q0.z), v3(q0.w, q1.x, q1.y), ray.o, invDir, dirIsNeg, &t0);
-                bool ok1 = ref1 != kEmptyRef && slabPartialFlat(v3(q1.z, q1.w, q2.x), v3(q2.y, q2.z, q2.w), ray.o, invDir, dirIsNeg, &t1);
-                bool nearIs1 = axis == 0 ? dirIsNeg[0] : (axis == 1 ? dirIsNeg[1] : dirIsNeg[2]);
+                // dirIsNeg (bvh.cpp:667-668) from the signs of invDir; both slab tests run unconditionally (an empty child --
+                // only the second child of record 0 -- is masked afterwards), so t0 / t1 stay in registers
+                const bool negX = invDir.x < 0, negY = invDir.y < 0, negZ = invDir.z < 0;
+                float t0 = 0, t1 = 0;
+                bool ok0 = slabPartialFlat(v3(q0.x, q0.y, q0.z), v3(q0.w, q1.x, q1.y), ray.o, invDir, negX, negY, negZ, &t0);
+                bool ok1 = slabPartialFlat(v3(q1.z, q1.w, q2.x), v3(q2.y, q2.z, q2.w), ray.o, invDir, negX, negY, negZ, &t1);
+                ok0 = ok0 & (ref0 != kEmptyRef);
+                ok1 = ok1 & (ref1 != kEmptyRef);
+                bool nearIs1 = axis == 0 ? negX : (axis == 1 ? negY : negZ);
                 int refNear = nearIs1 ? ref1 : ref0, refFar = nearIs1 ? ref0 : ref1;
                 bool okNear = nearIs1 ? ok1 : ok0, okFar = nearIs1 ? ok0 : ok1;
                 float tNear = nearIs1 ? t1 : t0, tFar = nearIs1 ? t0 : t1;

@@ -82,8 +82,7 @@ __device__ __forceinline__ void tracePersistent(const DevBVH &bvh, Source source
                                                 int phaseBias, TraverseCounters *cnt, Sink sink) {
     const unsigned kFull = 0xffffffffu;
     const int lane = threadIdx.x & 31;
-    int stackRef[64];
-    float stackT[64];
+    int2 stack[64];  // {ref, bits of the entry distance}: one 8-byte local access per push / pop
     // ref >= 0: interior record to visit; ref < 0: ~ref is the next primitive slot to test; kEmptyRef: no ray
     int sp = 0, ref = kEmptyRef, idx = -1, kind = MODE == kTraceAny ? 1 : 0;
     Ray ray;
@@ -160,10 +159,7 @@ __device__ __forceinline__ void tracePersistent(const DevBVH &bvh, Source source
                 bool okNear = nearIs1 ? ok1 : ok0, okFar = nearIs1 ? ok0 : ok1;
                 float tNear = nearIs1 ? t1 : t0, tFar = nearIs1 ? t0 : t1;
                 if (okFar) {
-                    if (sp > 0) {
-                        stackRef[sp - 1] = topRef;
-                        stackT[sp - 1] = topT;
-                    }
+                    if (sp > 0) stack[sp - 1] = make_int2(topRef, __float_as_int(topT));
                     topRef = refFar;
                     topT = tFar;
                     ++sp;
@@ -212,8 +208,9 @@ __device__ __forceinline__ void tracePersistent(const DevBVH &bvh, Source source
                 int r = topRef;
                 float t = topT;
                 if (sp > 0) {
-                    topRef = stackRef[sp - 1];
-                    topT = stackT[sp - 1];
+                    int2 e = stack[sp - 1];
+                    topRef = e.x;
+                    topT = __int_as_float(e.y);
                 }
                 if (t < ray.tMax) {
                     ref = r;

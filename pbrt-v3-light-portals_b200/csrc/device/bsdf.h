@@ -47,7 +47,8 @@ struct MatLobes {  // what ComputeScatteringFunctions adds for one material (bsd
     int nLobes;
     float eta;       // BSDF::eta
     int dispersive;  // eta (and every lobe's etaT) follows the path's wavelength
-    int shadeClass;  // 0: one Lambertian lobe; 1: anything else -- the hit queue is split by it (render.cu:splitHits)
+    int shadeClass;  // 0: one Lambertian lobe; 2: every lobe is specular (no light sampling: integrator.cpp:109-111 finds no
+                     // non-specular component); 1: anything else -- the hit queue is split by it (render.cu:splitHits)
     Lobe lobes[kMaxLobes];
 };
 

@@ -68,10 +68,12 @@ struct pbrtgpu_ctx {
     // trace kernel variant (tuning knobs, env PBRTGPU_TRACE_PERSISTENT / _FETCH_THRESHOLD / _PERSIST_BLOCKS)
     bool tracePersistent = true;
     bool traceFused = true;   // one traversal launch per depth for path + next-event + shadow rays
+    bool traceSharedScene = true;  // ... which stages the whole scene in shared memory when it fits (trace_persistent.h: kSharedSceneBytes)
     bool shadeSync = true;
     int lightStageBlocksPerSM = 16;  // grid of k_split_hits / k_post_trace, in 128-thread blocks per SM
     bool extPortalStrategy = false;  // a portal light of the uploaded scene uses a strategy the reference does not have
-    bool sortHits = true;       // hit queue split by material class (render.cu:splitHits)
+    int sortHits = 2;           // hit queue split by material class (render.cu:splitHits): 0 = off, 1 = Lambert | rest, 2 = Lambert | rest | all-specular
+    bool hasSpecularOnlyMaterial = false;  // some material of the uploaded scene is MatLobes::shadeClass 2
     bool shadeLambert = true;   // the front run of the split queue is shaded by the Lambert instantiation of the shade kernel
     int lambertBlock = 5122;    // its block shape: 5122 = 512 threads x 2 per SM, 5121, 3842, 2563, 2562 (A/B knob)
     bool hasPortalLight = false;

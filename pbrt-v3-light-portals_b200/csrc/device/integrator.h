@@ -22,6 +22,7 @@ struct WaveCounters {
     int nHit[kMaxDepthSlots];         // of the nActive[d] rays: how many hit something (queue hitIdx) ...
     int nMiss[kMaxDepthSlots];        // ... and how many escaped (queue missIdx)
     int nHitB[kMaxDepthSlots];        // hits on multi-lobe materials, kept apart: they fill hitIdx from its END downwards (render.cu:splitHits)
+    int nHitC[kMaxDepthSlots];        // hits on all-specular materials (MatLobes::shadeClass 2): they fill missIdx from its END downwards
     int fetch[3][kMaxDepthSlots];     // persistent trace kernels: next unclaimed queue position {closest, shadow, nee}
     int nNeeCulled[kMaxDepthSlots];   // MIS rays not traced because they miss the sampled light's shape (bvh.h:primitiveAccepts)
     unsigned long long cameraRays, closestRays, shadowRays, scrubbed;
@@ -78,7 +79,7 @@ struct WaveParams {
     unsigned char *shadowOcc;
     WaveCounters *cnt;
     int skipWavelength;    // no dispersive material: the camera sample's wavelength dimension is stepped over, not computed
-    int sortHits;          // split the hit queue by material class (single-lobe / multi-lobe) so that a warp shades one class
+    int sortHits;          // split the hit queue by material class so that a warp shades one class: 1 = Lambert | rest, 2 = ... | all-specular
     int phaseBias;         // persistent trace kernels: box-test rounds vs primitive-test rounds, see trace_persistent.h
     int fetchThreshold;    // persistent trace kernels refill a warp when this many lanes are idle
     unsigned long long *countTraversal;  // profile mode: {closest, shadow, nee} x {node tests, prim tests}; else null

@@ -107,7 +107,10 @@ static_assert(sizeof(ShadeScratch) == 37 * 4, "ShadeScratch must stay an odd num
 // the front run of the hit queue) or on a primitive without a material; the BSDF calls are the closed forms of
 // bsdf_eval.h (same arithmetic, bit-identical results), and nothing of the lobe machinery is compiled in.
 // PORTAL = false: the scene has no portal light; the portal estimators are not compiled in.
-template <class Sync, bool EXT = true, bool LAMBERT = false, bool PORTAL = true>
+// SPEC: every vertex handed in lies on a material all of whose lobes are specular (MatLobes::shadeClass 2: smooth glass, mirror).
+// UniformSampleOneLight is not called for it (path.cpp:121: NumComponents(BSDF_ALL & ~BSDF_SPECULAR) == 0), so phases 2-6 -- and
+// their barriers -- are not compiled in; what remains is the general code, expression for expression.
+template <class Sync, bool EXT = true, bool LAMBERT = false, bool PORTAL = true, bool SPEC = false>
 PG_HD void stageShadePhased(const WaveParams &w, int depth, int cur, int pos, bool active, Sync sync, ShadeScratch &scr) {
     const int flagsNS = BSDF_ALL & ~BSDF_SPECULAR;
     // ---- phase 0: path state, the hit record -> SurfaceInteraction, emitted light (path.cpp:91-96)
@@ -160,7 +163,7 @@ PG_HD void stageShadePhased(const WaveParams &w, int depth, int cur, int pos, bo
     sync(1);
 
     // ---- phase 2: UniformSampleOneLight's samples and light pick (integrator.cpp:100-122)
-    bool nee = scatter && (LAMBERT || bsdfNumComponents(bsdf, flagsNS) > 0) && w.sc.nLights > 0;
+    bool nee = !SPEC && scatter && (LAMBERT || bsdfNumComponents(bsdf, flagsNS) > 0) && w.sc.nLights > 0;
     int li = 0, lightTag = 0;
     float pickPdf = 0, uL0 = 0, uL1 = 0, uS0 = 0, uS1 = 0;
     if (nee) {
@@ -174,7 +177,7 @@ PG_HD void stageShadePhased(const WaveParams &w, int depth, int cur, int pos, bo
         get2D(w.hal, smp, &uS0, &uS1);
         lightTag = PG_LD(w.sc.lightTag + li);
     }
-    sync(2);
+    if (!SPEC) sync(2);
 
     // ---- phase 3: sample the light (EstimateDirect, integrator.cpp:133-141); portal lights take their own estimator
     const bool portal = PORTAL && nee && lightTag == PBRTGPU_LIGHT_PORTAL_AREA;
@@ -201,7 +204,7 @@ PG_HD void stageShadePhased(const WaveParams &w, int depth, int cur, int pos, bo
     }
     if (stock) Li = lightSampleLi(w.sc, li, it, uL0, uL1, &wi, &lightPdf, &pL);
     if (stock) PG_TRACE("  light d=%d slot=%d dim=%d li=%d uL=(%.9g %.9g) uS=(%.9g %.9g) wi=(%.9g %.9g %.9g) pdf=%.9g Li=(%.9g %.9g %.9g) pL=(%.9g %.9g %.9g)\n", depth, slot, smp.dim, li, uL0, uL1, uS0, uS1, wi.x, wi.y, wi.z, lightPdf, Li.r, Li.g, Li.b, pL.p.x, pL.p.y, pL.p.z);
-    sync(3);
+    if (!SPEC) sync(3);
 
     // ---- phase 4: BSDF value and pdf for the light sample; the shadow ray (integrator.cpp:142-184)
     if (stock && lightPdf > 0 && !isBlack(Li)) {
@@ -219,7 +222,7 @@ PG_HD void stageShadePhased(const WaveParams &w, int depth, int cur, int pos, bo
             PG_TRACE("  shadow d=%d slot=%d f=(%.9g %.9g %.9g) spdf=%.9g c=(%.9g %.9g %.9g) o=(%.9g %.9g %.9g) d=(%.9g %.9g %.9g)\n", depth, slot, f.r, f.g, f.b, scatteringPdf, c.r, c.g, c.b, sr.o.x, sr.o.y, sr.o.z, sr.d.x, sr.d.y, sr.d.z);
         }
     }
-    sync(4);
+    if (!SPEC) sync(4);
 
     // ---- phase 5: sample the BSDF for MIS (integrator.cpp:187-207)
     bool misRay = stock && !isDelta;
@@ -233,7 +236,7 @@ PG_HD void stageShadePhased(const WaveParams &w, int depth, int cur, int pos, bo
         sampledSpecular = (sampledType & BSDF_SPECULAR) != 0;
         misRay = !isBlack(fMis) && scatteringPdf > 0;
     }
-    sync(5);
+    if (!SPEC) sync(5);
 
     // ---- phase 6: the light's pdf for that direction; the MIS ray (integrator.cpp:208-254)
     if (misRay) {
@@ -261,7 +264,7 @@ PG_HD void stageShadePhased(const WaveParams &w, int depth, int cur, int pos, bo
             w.neeInfo[2 * (size_t)np + 1] = NEE_MIS_LIGHT;
         }
     }
-    sync(6);
+    if (!SPEC) sync(6);
 
     // ---- phase 7: sample the BSDF for the next direction (path.cpp:131-151)
     V3 wo = v3(0, 0, 0);
@@ -316,6 +319,11 @@ PG_HD void stageShade(const WaveParams &w, int depth, int cur, int pos) {
 PG_HD void stageShadeLambert(const WaveParams &w, int depth, int cur, int pos) {
     ShadeScratch scr;
     stageShadePhased<NoSync, true, true, true>(w, depth, cur, pos, true, NoSync(), scr);
+}
+// the all-specular instantiation (MatLobes::shadeClass 2)
+PG_HD void stageShadeSpecular(const WaveParams &w, int depth, int cur, int pos) {
+    ShadeScratch scr;
+    stageShadePhased<NoSync, true, false, true, true>(w, depth, cur, pos, true, NoSync(), scr);
 }
 
 // ---- stage 3 for Integrator "directlighting": DirectLightingIntegrator::Li (directlighting.cpp:63-98)

@@ -165,7 +165,11 @@ inline void buildMaterialLobes(const pbrtgpu_scene *s, std::vector<MatLobes> *ou
         const float *mp = s->mat_params + (size_t)i * PBRTGPU_MAT_STRIDE;
         makeMaterialLobes(s->mat_tag[i], mp, true, &(*out)[i]);
         makeMaterialLobes(s->mat_tag[i], mp, false, &(*out)[n + i]);
-        for (MatLobes *m : {&(*out)[i], &(*out)[n + i]}) m->shadeClass = (m->nLobes == 1 && m->lobes[0].kind == LOBE_LAMBERT) ? 0 : 1;
+        for (MatLobes *m : {&(*out)[i], &(*out)[n + i]}) {
+            bool allSpecular = m->nLobes > 0;
+            for (int k = 0; k < m->nLobes; ++k) allSpecular = allSpecular && (m->lobes[k].type & BSDF_SPECULAR) != 0;
+            m->shadeClass = (m->nLobes == 1 && m->lobes[0].kind == LOBE_LAMBERT) ? 0 : (allSpecular ? 2 : 1);
+        }
     }
 }
 // Specular-transmission lobes per material under allowMultipleLobes = false: 0 everywhere = directlighting's

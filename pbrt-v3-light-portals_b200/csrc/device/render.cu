@@ -81,13 +81,18 @@ __global__ void __launch_bounds__(kTraceBlock) k_trace_closest(WaveParams w, int
 // Persistent variants (trace_persistent.h): same results, rays handed to lanes dynamically.
 // They only record what was hit; queue compaction and the resolve arithmetic run as
 // separate dense kernels (few lanes finish a ray in the same round).
-template <bool COUNT>
-__global__ void __launch_bounds__(kTraceBlock, kPersistMinBlocks) k_ptrace_closest(WaveParams w, int depth, int cur) {
+// SMEM: the scene's records and primitive slots are staged into shared memory by every block (trace_persistent.h:
+// stageSceneShared; scenes of at most kSharedSceneBytes), nRecords = interior records of the device layout.
+template <bool COUNT, bool SMEM = false>
+__global__ void __launch_bounds__(kTraceBlock, kPersistMinBlocks) k_ptrace_closest(WaveParams w, int depth, int cur, int nRecords) {
     TraverseCounters c = {0, 0};
-    tracePersistent<kTraceClosest, COUNT>(w.sc.bvh, SingleQueue{w.rays[cur], 0}, w.cnt->nActive[depth], &w.cnt->fetch[0][depth],
-                                          w.fetchThreshold, w.phaseBias, &c, [&](int i, int, const Ray &, const Hit &h, bool) {
-                                              w.hits[i] = f4(__int_as_float(h.prim), h.b0, h.b1, h.b2);
-                                          });
+    auto sink = [&](int i, int, const Ray &, const Hit &h, bool) { w.hits[i] = f4(__int_as_float(h.prim), h.b0, h.b1, h.b2); };
+    if (SMEM)
+        tracePersistentFrom<kTraceClosest, COUNT>(w.sc.bvh, stageSceneShared(w.sc.bvh, nRecords, w.sc.nPrims), SingleQueue{w.rays[cur], 0},
+                                                  w.cnt->nActive[depth], &w.cnt->fetch[0][depth], w.fetchThreshold, w.phaseBias, &c, sink);
+    else
+        tracePersistent<kTraceClosest, COUNT>(w.sc.bvh, SingleQueue{w.rays[cur], 0}, w.cnt->nActive[depth], &w.cnt->fetch[0][depth],
+                                              w.fetchThreshold, w.phaseBias, &c, sink);
     flushCounts<COUNT>(w, 0, c);
 }
 
@@ -117,17 +122,21 @@ struct FusedQueue {
 __device__ __forceinline__ int neeQueueLen(const WaveParams &w, int depth) { return min(w.cnt->nNee[depth], w.neeCapacity); }
 __device__ __forceinline__ int shadowQueueLen(const WaveParams &w, int depth) { return min(w.cnt->nShadow[depth], w.neeCapacity); }
 
-template <bool COUNT>
-__global__ void __launch_bounds__(kTraceBlock, kPersistMinBlocks) k_ptrace_fused(WaveParams w, int depth, int cur) {
+template <bool COUNT, bool SMEM = false>
+__global__ void __launch_bounds__(kTraceBlock, kPersistMinBlocks) k_ptrace_fused(WaveParams w, int depth, int cur, int nRecords) {
     TraverseCounters c[3] = {{0, 0}, {0, 0}, {0, 0}};
     const int nPath = w.cnt->nActive[depth + 1], nNee = neeQueueLen(w, depth), nShadow = shadowQueueLen(w, depth);
     FusedQueue q = {w.rays[cur ^ 1], w.neeRays, w.shadowRays, nPath, nNee};
-    tracePersistent<kTraceMixed, COUNT>(w.sc.bvh, q, nPath + nNee + nShadow, &w.cnt->fetch[1][depth], w.fetchThreshold, w.phaseBias, c,
-                                        [&](int i, int kind, const Ray &, const Hit &h, bool found) {
-                                            if (kind == 0) w.hits[i] = f4(__int_as_float(h.prim), h.b0, h.b1, h.b2);
-                                            else if (kind == 2) w.neeHits[i - nPath] = f4(__int_as_float(h.prim), h.b0, h.b1, h.b2);
-                                            else w.shadowOcc[i - nPath - nNee] = found ? 1 : 0;
-                                        });
+    auto sink = [&](int i, int kind, const Ray &, const Hit &h, bool found) {
+        if (kind == 0) w.hits[i] = f4(__int_as_float(h.prim), h.b0, h.b1, h.b2);
+        else if (kind == 2) w.neeHits[i - nPath] = f4(__int_as_float(h.prim), h.b0, h.b1, h.b2);
+        else w.shadowOcc[i - nPath - nNee] = found ? 1 : 0;
+    };
+    if (SMEM)
+        tracePersistentFrom<kTraceMixed, COUNT>(w.sc.bvh, stageSceneShared(w.sc.bvh, nRecords, w.sc.nPrims), q, nPath + nNee + nShadow,
+                                                &w.cnt->fetch[1][depth], w.fetchThreshold, w.phaseBias, c, sink);
+    else
+        tracePersistent<kTraceMixed, COUNT>(w.sc.bvh, q, nPath + nNee + nShadow, &w.cnt->fetch[1][depth], w.fetchThreshold, w.phaseBias, c, sink);
     flushCounts<COUNT>(w, 0, c[0]);
     flushCounts<COUNT>(w, 1, c[1]);
     flushCounts<COUNT>(w, 2, c[2]);
@@ -137,24 +146,31 @@ __global__ void __launch_bounds__(kTraceBlock, kPersistMinBlocks) k_ptrace_fused
 // Hits on plain Lambertian materials fill hitIdx from the front, hits on everything else (plastic, uber, glass,
 // metal: microfacet or specular lobes, several lobes of which one is picked per sample) from the back: the
 // shade kernel walks the two runs one after the other, so all but one of its warps shade a single class
-// instead of every warp paying for the longest branch of a mixed one.
+// instead of every warp paying for the longest branch of a mixed one.  A third run holds the hits on materials all of whose
+// lobes are specular (smooth glass, mirror): they never sample a light, so their instantiation of the shade kernel has four
+// phases instead of nine, and they no longer halve the lanes of the warps that shade rough glass or plastic.  That run fills
+// missIdx from its end downwards (hits + misses = queue length <= nSlots, so the two ends never meet).
 __device__ __forceinline__ void splitHits(const WaveParams &w, int depth, bool wantMiss, int i) {
     int prim = __float_as_int(w.hits[i].x);
     if (prim >= 0) {
-        bool multi = false;
+        int cls = 0;
         if (w.sortHits && w.sc.primMaterial) {
             int m = __ldg(w.sc.primMaterial + prim);
-            if (m >= 0) multi = __ldg(&w.sc.matLobes[m].shadeClass) != 0;
+            if (m >= 0) cls = __ldg(&w.sc.matLobes[m].shadeClass);
+            if (cls == 2 && w.sortHits < 2) cls = 1;  // sortHits 1: two runs only (A/B)
         }
-        if (multi) w.hitIdx[w.nSlots - 1 - atomicIncInt(&w.cnt->nHitB[depth])] = i;
+        if (cls == 1) w.hitIdx[w.nSlots - 1 - atomicIncInt(&w.cnt->nHitB[depth])] = i;
+        else if (cls == 2) w.missIdx[w.nSlots - 1 - atomicIncInt(&w.cnt->nHitC[depth])] = i;
         else w.hitIdx[atomicIncInt(&w.cnt->nHit[depth])] = i;
     } else if (wantMiss)
         w.missIdx[atomicIncInt(&w.cnt->nMiss[depth])] = i;
 }
-__device__ __forceinline__ int hitQueueLen(const WaveParams &w, int depth) { return w.cnt->nHit[depth] + w.cnt->nHitB[depth]; }
+__device__ __forceinline__ int hitQueueLen(const WaveParams &w, int depth) { return w.cnt->nHit[depth] + w.cnt->nHitB[depth] + w.cnt->nHitC[depth]; }
 __device__ __forceinline__ int hitQueueAt(const WaveParams &w, int depth, int i) {
-    int nA = w.cnt->nHit[depth];
-    return i < nA ? w.hitIdx[i] : w.hitIdx[w.nSlots - 1 - (i - nA)];
+    int nA = w.cnt->nHit[depth], nB = w.cnt->nHitB[depth];
+    if (i < nA) return w.hitIdx[i];
+    if (i < nA + nB) return w.hitIdx[w.nSlots - 1 - (i - nA)];
+    return w.missIdx[w.nSlots - 1 - (i - nA - nB)];
 }
 __global__ void __launch_bounds__(kStageBlock) k_split_hits(WaveParams w, int depth, bool wantMiss) {
     int n = w.cnt->nActive[depth];
@@ -223,12 +239,13 @@ struct BlockSync {
 };
 // EXT: with the non-reference portal strategies (direct.h).  LAMBERT / PORTAL: see stageShadePhased.
 // run: which part of the hit queue -- 0 = all of it, 1 = the front run (hits on single-Lambert-lobe materials and on
-// material-less primitives, render.cu:splitHits), 2 = the back run (every other material).
-template <int BLOCK, int PER_SM, bool EXT = false, bool LAMBERT = false, bool PORTAL = true>
+// material-less primitives, render.cu:splitHits), 2 = the back run (every other material but the all-specular ones),
+// 3 = the all-specular run (SPEC).
+template <int BLOCK, int PER_SM, bool EXT = false, bool LAMBERT = false, bool PORTAL = true, bool SPEC = false>
 __global__ void __launch_bounds__(BLOCK, PER_SM) k_shade_sync(const WaveParams *__restrict__ wp, int depth, int cur, int run) {
     const WaveParams &w = *wp;
-    const int nA = w.cnt->nHit[depth], nB = w.cnt->nHitB[depth];
-    const int begin = run == 2 ? nA : 0, end = run == 1 ? nA : nA + nB;
+    const int nA = w.cnt->nHit[depth], nB = w.cnt->nHitB[depth], nC = w.cnt->nHitC[depth];
+    const int begin = run == 2 ? nA : (run == 3 ? nA + nB : 0), end = run == 1 ? nA : (run == 2 ? nA + nB : nA + nB + nC);
     int stride = gridDim.x * blockDim.x;
 #ifdef PG_SHADE_LOCAL_SCRATCH
     ShadeScratch scr;
@@ -239,7 +256,7 @@ __global__ void __launch_bounds__(BLOCK, PER_SM) k_shade_sync(const WaveParams *
     for (int base = begin + blockIdx.x * blockDim.x; base < end; base += stride) {
         int i = base + threadIdx.x;
         bool active = i < end;
-        stageShadePhased<BlockSync, EXT, LAMBERT, PORTAL>(w, depth, cur, active ? hitQueueAt(w, depth, i) : 0, active, BlockSync(), scr);
+        stageShadePhased<BlockSync, EXT, LAMBERT, PORTAL, SPEC>(w, depth, cur, active ? hitQueueAt(w, depth, i) : 0, active, BlockSync(), scr);
     }
 }
 
@@ -312,13 +329,13 @@ __global__ void k_batch_stats(WaveCounters *cnt, unsigned long long *totals, int
     totals[3] += cnt->scrubbed;
     totals[6] += cnt->dropped;
     const int a = cnt->nActive[depths], h = depths < kMaxDepthSlots ? cnt->nHit[depths] : 0, m = depths < kMaxDepthSlots ? cnt->nMiss[depths] : 0;
-    const int hb = depths < kMaxDepthSlots ? cnt->nHitB[depths] : 0;
+    const int hb = depths < kMaxDepthSlots ? cnt->nHitB[depths] : 0, hc = depths < kMaxDepthSlots ? cnt->nHitC[depths] : 0;
     for (int d = 0; d <= kMaxDepthSlots; ++d) cnt->nActive[d] = 0;
     for (int d = 0; d < kMaxDepthSlots; ++d)
-        cnt->nShadow[d] = cnt->nNee[d] = cnt->nHit[d] = cnt->nHitB[d] = cnt->nMiss[d] = cnt->fetch[0][d] = cnt->fetch[1][d] = cnt->fetch[2][d] = cnt->nNeeCulled[d] = 0;
+        cnt->nShadow[d] = cnt->nNee[d] = cnt->nHit[d] = cnt->nHitB[d] = cnt->nHitC[d] = cnt->nMiss[d] = cnt->fetch[0][d] = cnt->fetch[1][d] = cnt->fetch[2][d] = cnt->nNeeCulled[d] = 0;
     cnt->scrubbed = 0;
     cnt->dropped = 0;
-    if (carry) cnt->nActive[0] = a, cnt->nHit[0] = h, cnt->nHitB[0] = hb, cnt->nMiss[0] = m;
+    if (carry) cnt->nActive[0] = a, cnt->nHit[0] = h, cnt->nHitB[0] = hb, cnt->nHitC[0] = hc, cnt->nMiss[0] = m;
 }
 
 // Film::MergeFilmTile's RGB -> XYZ (film.cpp:125-127), once per pixel at the end

@@ -77,9 +77,40 @@ struct SingleQueue {  // one ray array, one kind
     }
 };
 
-template <int MODE, bool COUNT, class Source, class Sink>
-__device__ __forceinline__ void tracePersistent(const DevBVH &bvh, Source source, int n, int *next, int fetchThreshold,
-                                                int phaseBias, TraverseCounters *cnt, Sink sink) {
+// Where a round's interior record / primitive slot comes from.  GlobalFetch: the scene arrays through the read-only path
+// (L1 / L2).  SharedFetch: a copy of BOTH arrays that the block staged into shared memory at kernel start (stageSceneShared);
+// only scenes whose records and slots fit kSharedSceneBytes qualify (the Cornell box: 20 records + 32 slots = 2.8 KB) --
+// every fetch of a round is then one LDS.128 and the L1 is left to the ray queues.
+constexpr int kSharedSceneBytes = 16 * 1024;  // per block; 8 resident blocks per SM
+struct GlobalFetch {
+    const F4 *nodes, *tris;
+    __device__ __forceinline__ F4 node(size_t i) const { return __ldg(nodes + i); }
+    __device__ __forceinline__ F4 tri(size_t i) const { return __ldg(tris + i); }
+};
+struct SharedFetch {
+    int triBase;  // in F4: the primitive slots follow the records
+    __device__ __forceinline__ F4 node(size_t i) const {
+        extern __shared__ __align__(16) F4 pgSceneSmem[];
+        return pgSceneSmem[i];
+    }
+    __device__ __forceinline__ F4 tri(size_t i) const {
+        extern __shared__ __align__(16) F4 pgSceneSmem[];
+        return pgSceneSmem[triBase + i];
+    }
+};
+// every thread of the block calls this before tracePersistent
+__device__ __forceinline__ SharedFetch stageSceneShared(const DevBVH &bvh, int nRecords, int nSlots) {
+    extern __shared__ __align__(16) F4 pgSceneSmem[];
+    const int nN = 4 * nRecords, nT = 3 * nSlots;
+    for (int i = threadIdx.x; i < nN; i += blockDim.x) pgSceneSmem[i] = __ldg(bvh.nodes + i);
+    for (int i = threadIdx.x; i < nT; i += blockDim.x) pgSceneSmem[nN + i] = __ldg(bvh.tris + i);
+    __syncthreads();
+    return SharedFetch{nN};
+}
+
+template <int MODE, bool COUNT, class Fetch, class Source, class Sink>
+__device__ __forceinline__ void tracePersistentFrom(const DevBVH &bvh, Fetch fetch, Source source, int n, int *next, int fetchThreshold,
+                                                    int phaseBias, TraverseCounters *cnt, Sink sink) {
     const unsigned kFull = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     int2 stack[64];  // {ref, bits of the entry distance}: one 8-byte local access per push / pop
@@ -142,8 +173,8 @@ __device__ __forceinline__ void tracePersistent(const DevBVH &bvh, Source source
         if (nI > 0 && 16 * nI >= phaseBias * nP) {
             // ---- one interior record: both children's bounds
             if (atInterior) {
-                const F4 *nd = bvh.nodes + 4 * (size_t)ref;
-                F4 q0 = __ldg(nd), q1 = __ldg(nd + 1), q2 = __ldg(nd + 2), q3 = __ldg(nd + 3);
+                const size_t nd = 4 * (size_t)ref;
+                F4 q0 = fetch.node(nd), q1 = fetch.node(nd + 1), q2 = fetch.node(nd + 2), q3 = fetch.node(nd + 3);
                 if (COUNT) cnt[MODE == kTraceMixed ? kind : 0].nodes += 2;
                 int ref0 = f2i(q3.x), ref1 = f2i(q3.y), axis = f2i(q3.z);
                 // dirIsNeg (bvh.cpp:667-668) from the signs of invDir; both slab tests run unconditionally (an empty child --
@@ -170,15 +201,15 @@ __device__ __forceinline__ void tracePersistent(const DevBVH &bvh, Source source
         } else if (atPrim) {
             // ---- one primitive of the leaf
             int slot = ~ref;
-            const F4 *tp = bvh.tris + 3 * (size_t)slot;
-            F4 a = __ldg(tp);
+            const size_t tp = 3 * (size_t)slot;
+            F4 a = fetch.tri(tp);
             int tag = f2i(a.w);
             int type = tag & kTagTypeMask;
             if (COUNT) cnt[MODE == kTraceMixed ? kind : 0].prims += 1;
             float t, b0 = 0, b1 = 0, b2 = 0;
             bool h;
             if (type == 0) {
-                F4 b = __ldg(tp + 1), c = __ldg(tp + 2);
+                F4 b = fetch.tri(tp + 1), c = fetch.tri(tp + 2);
                 h = triangleTestSheared(ray, shear, v3(a.x, a.y, a.z), v3(b.x, b.y, b.z), v3(c.x, c.y, c.z), &t, &b0, &b1, &b2);
                 if (!any && (tag & kTagDegenerate)) h = false;
             } else if (type == 1) {
@@ -220,6 +251,12 @@ __device__ __forceinline__ void tracePersistent(const DevBVH &bvh, Source source
         }
         if ((atInterior || atPrim) && ref == kEmptyRef) sink(idx, kind, ray, hit, any ? occluded : hit.prim >= 0);
     }
+}
+
+template <int MODE, bool COUNT, class Source, class Sink>
+__device__ __forceinline__ void tracePersistent(const DevBVH &bvh, Source source, int n, int *next, int fetchThreshold,
+                                                int phaseBias, TraverseCounters *cnt, Sink sink) {
+    tracePersistentFrom<MODE, COUNT>(bvh, GlobalFetch{bvh.nodes, bvh.tris}, source, n, next, fetchThreshold, phaseBias, cnt, sink);
 }
 
 }  // namespace pg

@@ -77,11 +77,12 @@ int pbrtgpu_create(int cuda_device, pbrtgpu_ctx **out) {
     ctx->ownStream = true;
     cudaDeviceGetAttribute(&ctx->smCount, cudaDevAttrMultiProcessorCount, cuda_device);
     if (const char *v = getenv("PBRTGPU_TRACE_PERSISTENT")) ctx->tracePersistent = atoi(v) != 0;
+    if (const char *v = getenv("PBRTGPU_TRACE_SHARED_SCENE")) ctx->traceSharedScene = atoi(v) != 0;
     if (const char *v = getenv("PBRTGPU_TRACE_FUSED")) ctx->traceFused = atoi(v) != 0;
     if (const char *v = getenv("PBRTGPU_SHADE_SYNC")) ctx->shadeSync = atoi(v) != 0;
     if (const char *v = getenv("PBRTGPU_LIGHT_STAGE_BLOCKS")) ctx->lightStageBlocksPerSM = std::min(32, std::max(1, atoi(v)));
     if (const char *v = getenv("PBRTGPU_LAYOUT")) ctx->layoutOnDevice = strcmp(v, "host") != 0;
-    if (const char *v = getenv("PBRTGPU_SORT_HITS")) ctx->sortHits = atoi(v) != 0;
+    if (const char *v = getenv("PBRTGPU_SORT_HITS")) ctx->sortHits = atoi(v) < 0 ? 0 : (atoi(v) > 2 ? 2 : atoi(v));
     if (const char *v = getenv("PBRTGPU_SHADE_LAMBERT")) ctx->shadeLambert = atoi(v) != 0;
     if (const char *v = getenv("PBRTGPU_LAMBERT_BLOCK")) ctx->lambertBlock = atoi(v);
     if (const char *v = getenv("PBRTGPU_FETCH_THRESHOLD")) ctx->fetchThreshold = std::min(32, std::max(1, atoi(v)));
@@ -251,6 +252,9 @@ int pbrtgpu_upload_scene(pbrtgpu_ctx *ctx, const pbrtgpu_scene *s) {
         ctx->hasDispersiveMaterial = false;
         for (const MatLobes &m : lobes)
             if (m.dispersive) ctx->hasDispersiveMaterial = true;
+        ctx->hasSpecularOnlyMaterial = false;
+        for (int i = 0; i < s->n_materials; ++i)  // the path integrator's half of the table
+            if (lobes[i].shadeClass == 2) ctx->hasSpecularOnlyMaterial = true;
         ctx->maxSpecTransLobes = maxSpecularTransmissionLobes(lobes, s->n_materials, &ctx->specTransDispersive);
     }
     UP(s->light_portal_begin, s->light_portal_begin ? s->n_lights + 1 : 0, &d.lightPortalBegin);

@@ -215,6 +215,7 @@ extern "C" int hostsim_render(void *p, const pbrtgpu_render_params *rp, float *f
                             int prim = f2i(w.hits[w.hitIdx[i]].x);
                             int m = w.sc.primMaterial ? w.sc.primMaterial[prim] : -1;
                             if (m < 0 || w.sc.matLobes[m].shadeClass == 0) stageShadeLambert(w, d, cur, w.hitIdx[i]);
+                            else if (w.sc.matLobes[m].shadeClass == 2) stageShadeSpecular(w, d, cur, w.hitIdx[i]);  // all-specular materials
                             else stageShade(w, d, cur, w.hitIdx[i]);
                         } else stageShade(w, d, cur, w.hitIdx[i]);
                     }

@@ -601,7 +601,8 @@ def test_one_ulp_of_libm_moves_killeroo_samples(pkg, hostsim_lib, hostsim_pertur
 
 @pytest.mark.parametrize("case", ["box_glass", "portal_room_portal", "null_shells", "sphere_lights"])
 def test_lambert_shade_instantiation_is_bit_identical(pkg, hostsim_lib, case, monkeypatch):
-    """stageShadePhased<..., LAMBERT> (bsdf_eval.h: lambertF / lambertPdf / lambertSampleF) against the general BSDF
+    """stageShadePhased<..., LAMBERT> (bsdf_eval.h: lambertF / lambertPdf / lambertSampleF) and <..., SPEC> (materials all of
+    whose lobes are specular -- box_glass's glass, sphere_lights' mirror: no light sampling compiled in) against the general
     routines on the same vertices: one thread, so that even the order of additions into a pixel is the same -- the two
     films must be equal bit for bit."""
     hs = load_case(pkg, case)

@@ -115,6 +115,15 @@ struct FusedQueue {
         *ray = loadRayF4(q, idx);
         return kind;
     }
+    __device__ __forceinline__ void prefetch(int idx) const {
+        const F4 *q = path;
+        if (idx >= nPath) {
+            idx -= nPath;
+            q = nee;
+            if (idx >= nNee) idx -= nNee, q = shadow;
+        }
+        asm volatile("prefetch.global.L1 [%0];" ::"l"(q + 2 * (size_t)idx));
+    }
 };
 
 // Lengths of the light-sample queues as their consumers see them: a push past the capacity is counted

@@ -4,8 +4,9 @@
 // BVHAccel::Intersect / IntersectP, accelerators/bvh.cpp:662-738); only the
 // mapping of rays to lanes differs:
 //   * a warp keeps running until the ray queue is drained; a lane whose ray
-//     has finished picks up the next queued ray (one atomicAdd per warp and
-//     refill) instead of idling until the slowest ray of its warp is done;
+//     has finished picks up the next queued ray (queue positions are claimed 32
+//     at a time, one chunk ahead, their rays prefetched) instead of idling until
+//     the slowest ray of its warp is done;
 //   * every round of the loop the warp does ONE kind of work, chosen by a vote:
 //     either each lane that is at an interior record tests its two children,
 //     or each lane that is at a primitive tests it; box tests and triangle
@@ -75,6 +76,7 @@ struct SingleQueue {  // one ray array, one kind
         *ray = loadRayF4(rays, idx);
         return kind;
     }
+    __device__ __forceinline__ void prefetch(int idx) const { asm volatile("prefetch.global.L1 [%0];" ::"l"(rays + 2 * (size_t)idx)); }
 };
 
 // Where a round's interior record / primitive slot comes from.  GlobalFetch: the scene arrays through the read-only path
@@ -128,41 +130,49 @@ __device__ __forceinline__ void tracePersistentFrom(const DevBVH &bvh, Fetch fet
     hit.t = hit.b0 = hit.b1 = hit.b2 = 0;
     bool exhausted = false;  // warp-uniform: the queue has been handed out completely
     // The first 32 rays of every warp are assigned statically (queue positions [32 * warp, 32 * warp + 32));
-    // the shared cursor `next` hands out what lies beyond all warps' first chunks.  A launch over a short
-    // queue therefore costs no atomics at all.
+    // the shared cursor `next` hands out what lies beyond all warps' first chunks, 32 positions per atomicAdd.
+    // A launch over a short queue therefore costs no atomics at all.
     const int warpsInGrid = (gridDim.x * blockDim.x) >> 5;
     const int warpId = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int dynamicBegin = warpsInGrid * 32;
-    bool first = true;
-
+    // Queue positions are claimed one chunk AHEAD of their use: [aheadBase, aheadBase + aheadLeft) belongs to this warp and
+    // its rays are on their way into L1 (one prefetch per lane at claim time), so the ray loads of a refill -- 5 % of the
+    // kernel's stall samples in the r02l source profile, with every lane of the warp waiting -- find them there, and most
+    // refills need no atomic.  +1 % on killeroo, Cornell and the portal room (profiles/r02m_ab_trace_variants.log).
+    int aheadBase = warpId * 32, aheadLeft = 32;
     for (;;) {
         unsigned idle = __ballot_sync(kFull, ref == kEmptyRef);
         if (idle) {
             int nIdle = __popc(idle);
             if (!exhausted && nIdle >= fetchThreshold) {
-                int leader = __ffs(idle) - 1;
-                int base = 0;
-                if (first) {
-                    base = warpId * 32;
-                    first = false;
-                    if (dynamicBegin >= n) exhausted = true;  // nothing for the cursor to hand out
-                } else {
-                    if (lane == leader) base = dynamicBegin + atomicAdd(next, nIdle);
-                    base = __shfl_sync(kFull, base, leader);
-                }
-                if (ref == kEmptyRef) {
-                    int mine = base + __popc(idle & ((1u << lane) - 1));
-                    if (mine < n) {
-                        idx = mine;
-                        kind = source(idx, &ray);
-                        invDir = v3(1 / ray.d.x, 1 / ray.d.y, 1 / ray.d.z);
-                        shear = rayShear(ray.d);
-                        hit.prim = -1;
-                        sp = 0;
-                        ref = 0;
+                const int rank = __popc(idle & ((1u << lane) - 1));
+                const int k = min(nIdle, aheadLeft);
+                int mine = aheadBase + rank;  // lanes of rank < k take the rest of the claimed chunk
+                if (nIdle >= aheadLeft) {     // ... which is used up: claim the next one, lanes of rank >= k start it
+                    int nb = n;
+                    if (dynamicBegin < n) {
+                        if (lane == 0) nb = dynamicBegin + atomicAdd(next, 32);
+                        nb = __shfl_sync(kFull, nb, 0);
                     }
+                    if (rank >= k) mine = nb + (rank - k);
+                    aheadBase = nb + (nIdle - k);
+                    aheadLeft = 32 - (nIdle - k);
+                    const int p = aheadBase + lane;
+                    if (lane < aheadLeft && p < n) source.prefetch(p);
+                } else {
+                    aheadBase += k;
+                    aheadLeft -= k;
                 }
-                exhausted = exhausted || (base >= dynamicBegin && base + nIdle >= n);
+                if (ref == kEmptyRef && mine < n) {
+                    idx = mine;
+                    kind = source(idx, &ray);
+                    invDir = v3(1 / ray.d.x, 1 / ray.d.y, 1 / ray.d.z);
+                    shear = rayShear(ray.d);
+                    hit.prim = -1;
+                    sp = 0;
+                    ref = 0;
+                }
+                exhausted = aheadBase >= n;  // nothing claimed is left to start, and nothing is left to claim
             }
             if (exhausted && __all_sync(kFull, ref == kEmptyRef)) return;
         }

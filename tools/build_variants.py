@@ -17,16 +17,20 @@ b = importlib.import_module("pbrt-v3-light-portals_b200.build")
 
 
 def main():
+    import concurrent.futures
     out = os.path.join(b.OUT, "variants")
     os.makedirs(out, exist_ok=True)
     srcs = sorted(glob.glob(os.path.join(b.CSRC, "device", "*.cu")))
-    for arg in sys.argv[1:]:
+    def one(arg):
         name, flags = arg.split("=", 1)
         target = os.path.join(out, "libpbrtgpu_%s.so" % name)
         log = b._run(["nvcc"] + b.NVCC_FLAGS + flags.split() + ["-Xptxas", "-v", "-shared", "-I" + os.path.join(ROOT, "include")] + srcs +
                      ["-o", target, "-lcudart", "-lpthread"])
-        m = re.search(r"k_shade_syncILi1024ELi1.*?\n.*?\n\s*(\d+) bytes stack frame, (\d+) bytes spill stores, (\d+) bytes spill loads", log)
-        print(name, "->", target, "shade<1024>: stack %s spill st %s ld %s" % m.groups() if m else "")
+        open(target + ".ptxas.log", "w").write(log)
+        return name + " -> " + target
+    with concurrent.futures.ThreadPoolExecutor(max_workers=4) as ex:  # one nvcc per variant, side by side
+        for line in ex.map(one, sys.argv[1:]):
+            print(line)
 
 
 if __name__ == "__main__":

@@ -104,7 +104,7 @@ extern "C" int pbrtgpu_intersect_closest_noalloc(pbrtgpu_ctx *ctx, const float *
     PG_CUDA(ctx, cudaMemsetAsync(cursor, 0, kCursorBytes, ctx->stream));  // the one part that must start at zero
     PG_CUDA(ctx, cudaMemcpyAsync(dRays, rays, (size_t)m * 32, cudaMemcpyHostToDevice, ctx->stream));
     const int blocks = (int)std::min<long long>(((long long)m + kTraceBlock - 1) / kTraceBlock, (long long)ctx->smCount * ctx->persistBlocksPerSM);
-    k_pintersect_closest_static<<<blocks, kTraceBlock, kTraceStateSmem, ctx->stream>>>(ctx->scene, dRays, m, dHits, cursor, ctx->fetchThreshold, ctx->phaseBias);
+    k_pintersect_closest_static<<<blocks, kTraceBlock, 0, ctx->stream>>>(ctx->scene, dRays, m, dHits, cursor, ctx->fetchThreshold, ctx->phaseBias);
     k_split_hit_columns<<<std::min(ctx->smCount * 4, (m + 255) / 256), 256, 0, ctx->stream>>>(dHits, m, dIds, dT, dBary);
     ctx->launches += 2;
     PG_CUDA(ctx, cudaGetLastError());

@@ -88,14 +88,8 @@ __global__ void __launch_bounds__(kTraceBlock, kPersistMinBlocks) k_ptrace_close
     TraverseCounters c = {0, 0};
     auto sink = [&](int i, int, const Ray &, const Hit &h, bool) { w.hits[i] = f4(__int_as_float(h.prim), h.b0, h.b1, h.b2); };
     if (SMEM)
-#ifdef PG_TRACE_DUAL
-        tracePersistentDual<kTraceClosest, COUNT>(w.sc.bvh, stageSceneShared(w.sc.bvh, nRecords, w.sc.nPrims), 4 * nRecords + 3 * w.sc.nPrims,
-                                                  SingleQueue{w.rays[cur], 0}, w.cnt->nActive[depth], &w.cnt->fetch[0][depth], w.fetchThreshold,
-                                                  w.phaseBias, &c, sink);
-#else
         tracePersistentFrom<kTraceClosest, COUNT>(w.sc.bvh, stageSceneShared(w.sc.bvh, nRecords, w.sc.nPrims), SingleQueue{w.rays[cur], 0},
                                                   w.cnt->nActive[depth], &w.cnt->fetch[0][depth], w.fetchThreshold, w.phaseBias, &c, sink);
-#endif
     else
         tracePersistent<kTraceClosest, COUNT>(w.sc.bvh, SingleQueue{w.rays[cur], 0}, w.cnt->nActive[depth], &w.cnt->fetch[0][depth],
                                               w.fetchThreshold, w.phaseBias, &c, sink);
@@ -148,13 +142,8 @@ __global__ void __launch_bounds__(kTraceBlock, kPersistMinBlocks) k_ptrace_fused
         else w.shadowOcc[i - nPath - nNee] = found ? 1 : 0;
     };
     if (SMEM)
-#ifdef PG_TRACE_DUAL
-        tracePersistentDual<kTraceMixed, COUNT>(w.sc.bvh, stageSceneShared(w.sc.bvh, nRecords, w.sc.nPrims), 4 * nRecords + 3 * w.sc.nPrims, q,
-                                                nPath + nNee + nShadow, &w.cnt->fetch[1][depth], w.fetchThreshold, w.phaseBias, c, sink);
-#else
         tracePersistentFrom<kTraceMixed, COUNT>(w.sc.bvh, stageSceneShared(w.sc.bvh, nRecords, w.sc.nPrims), q, nPath + nNee + nShadow,
                                                 &w.cnt->fetch[1][depth], w.fetchThreshold, w.phaseBias, c, sink);
-#endif
     else
         tracePersistent<kTraceMixed, COUNT>(w.sc.bvh, q, nPath + nNee + nShadow, &w.cnt->fetch[1][depth], w.fetchThreshold, w.phaseBias, c, sink);
     flushCounts<COUNT>(w, 0, c[0]);

@@ -88,10 +88,10 @@ static int timedLaunch(pbrtgpu_ctx *ctx, bool any, const void *dRays, long long 
             long long blocks = std::min<long long>(((long long)m + kTraceBlock - 1) / kTraceBlock, (long long)ctx->smCount * ctx->persistBlocksPerSM);
             PG_CUDA(ctx, cudaMemsetAsync(ctx->dFetch, 0, sizeof(int), ctx->stream));
             if (any)
-                k_pintersect_any<<<(int)blocks, kTraceBlock, kTraceStateSmem, ctx->stream>>>(ctx->scene, (const float4 *)dRays + 2 * off, m,
+                k_pintersect_any<<<(int)blocks, kTraceBlock, 0, ctx->stream>>>(ctx->scene, (const float4 *)dRays + 2 * off, m,
                                                                                (unsigned char *)dOut + off, ctx->dFetch, ctx->fetchThreshold, ctx->phaseBias);
             else
-                k_pintersect_closest<<<(int)blocks, kTraceBlock, kTraceStateSmem, ctx->stream>>>(ctx->scene, (const float4 *)dRays + 2 * off, m,
+                k_pintersect_closest<<<(int)blocks, kTraceBlock, 0, ctx->stream>>>(ctx->scene, (const float4 *)dRays + 2 * off, m,
                                                                                    (float4 *)dOut + off, ctx->dFetch, ctx->fetchThreshold, ctx->phaseBias);
         }
     } else {

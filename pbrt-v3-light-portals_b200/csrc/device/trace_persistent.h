@@ -263,209 +263,11 @@ __device__ __forceinline__ void tracePersistentFrom(const DevBVH &bvh, Fetch fet
     }
 }
 
-// ---- Two rays per lane (PG_TRACE_DUAL).
-// The vote-scheduled loop above leaves a lane idle whenever its ray is at the other kind of work (or finished and waiting
-// for the next refill): 17-18 of 32 lanes per instruction on every scene measured.  Here every lane owns TWO ray slots.  The
-// per-ray state lives in shared memory (four float4 per slot, laid out [group][slot] with slot = k * blockDim + thread, so a
-// warp's access to one group is 32 consecutive float4: conflict-free LDS.128 / STS.128); only the two `ref` words stay in
-// registers.  A round still does one kind of work, chosen by a vote over all 64 slots of the warp, and each lane runs it for
-// whichever of its two rays stands at that kind -- a lane idles only if neither does.  A ray's own sequence of box tests,
-// primitive tests, pushes and pops is exactly the one of the loop above (the state it reads is the state it wrote), so the
-// results are bit-identical; the stacks are two local-memory arrays per thread.
-//   group 0: o.xyz, tMax          group 1: invDir.xyz, meta = sp | kz << 8 | kind << 12
-//   group 2: Sx, Sy, Sz, idx      group 3: hit prim, b0, b1, b2
-constexpr int kDualSlots = 2;
-constexpr int kDualGroups = 4;
-constexpr int kDualStack = 64;
-__host__ __device__ constexpr size_t dualStateBytes(int blockThreads) { return (size_t)kDualGroups * kDualSlots * blockThreads * 16; }
-
-template <int MODE, bool COUNT, class Fetch, class Source, class Sink>
-__device__ __forceinline__ void tracePersistentDual(const DevBVH &bvh, Fetch fetch, int stateBaseF4, Source source, int n, int *next,
-                                                    int fetchThreshold, int phaseBias, TraverseCounters *cnt, Sink sink) {
-    extern __shared__ __align__(16) F4 pgSceneSmem[];
-    F4 *const st = pgSceneSmem + stateBaseF4;
-    const int slotsPerGroup = kDualSlots * blockDim.x;
-    const unsigned kFull = 0xffffffffu;
-    const int lane = threadIdx.x & 31;
-    int2 stack[kDualSlots][kDualStack];
-    int refA = kEmptyRef, refB = kEmptyRef;
-    bool exhausted = false;
-    const int warpsInGrid = (gridDim.x * blockDim.x) >> 5;
-    const int warpId = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const int dynamicBegin = warpsInGrid * 32;
-    int aheadBase = warpId * 32, aheadLeft = 32;  // claimed ahead, as above
-    unsigned round = 0;
-
-    for (;;) {
-        const bool eA = refA == kEmptyRef, eB = refB == kEmptyRef;
-        const unsigned idle = __ballot_sync(kFull, eA || eB);  // lanes with a free slot; a refill fills one slot per lane
-        if (idle) {
-            const int nIdle = __popc(idle);
-            if (!exhausted && nIdle >= fetchThreshold) {
-                const int rank = __popc(idle & ((1u << lane) - 1));
-                const int k = min(nIdle, aheadLeft);
-                int mine = aheadBase + rank;
-                if (nIdle >= aheadLeft) {
-                    int nb = n;
-                    if (dynamicBegin < n) {
-                        if (lane == 0) nb = dynamicBegin + atomicAdd(next, 32);
-                        nb = __shfl_sync(kFull, nb, 0);
-                    }
-                    if (rank >= k) mine = nb + (rank - k);
-                    aheadBase = nb + (nIdle - k);
-                    aheadLeft = 32 - (nIdle - k);
-                    const int p = aheadBase + lane;
-                    if (lane < aheadLeft && p < n) source.prefetch(p);
-                } else {
-                    aheadBase += k;
-                    aheadLeft -= k;
-                }
-                if ((eA || eB) && mine < n) {
-                    Ray ray;
-                    const int kind = source(mine, &ray);
-                    const V3 invDir = v3(1 / ray.d.x, 1 / ray.d.y, 1 / ray.d.z);
-                    const RayShear shear = rayShear(ray.d);
-                    const int s = (eA ? 0 : blockDim.x) + threadIdx.x;
-                    st[s] = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.tMax);
-                    st[slotsPerGroup + s] = make_float4(invDir.x, invDir.y, invDir.z, __int_as_float((shear.kz << 8) | (kind << 12)));
-                    st[2 * slotsPerGroup + s] = make_float4(shear.Sx, shear.Sy, shear.Sz, __int_as_float(mine));
-                    st[3 * slotsPerGroup + s] = make_float4(__int_as_float(-1), 0.f, 0.f, 0.f);
-                    if (eA) refA = 0;
-                    else refB = 0;
-                }
-                exhausted = aheadBase >= n;
-            }
-            if (exhausted && __all_sync(kFull, refA == kEmptyRef && refB == kEmptyRef)) return;
-        }
-        const bool iA = refA >= 0, iB = refB >= 0;
-        const bool pA = refA < 0 && refA != kEmptyRef, pB = refB < 0 && refB != kEmptyRef;
-        const int nI = __popc(__ballot_sync(kFull, iA)) + __popc(__ballot_sync(kFull, iB));
-        const int nP = __popc(__ballot_sync(kFull, pA)) + __popc(__ballot_sync(kFull, pB));
-        const bool box = nI > 0 && 16 * nI >= phaseBias * nP;
-        const bool mA = box ? iA : pA, mB = box ? iB : pB;
-        ++round;
-        if (mA || mB) {
-        const int k = (mA && mB) ? (int)(round & 1) : (mA ? 0 : 1);  // both qualify: take turns
-        const int s = k * blockDim.x + threadIdx.x;
-        int ref = k ? refB : refA;
-        const F4 s0 = st[s];
-        const V3 o = v3(s0.x, s0.y, s0.z);
-        float tMax = s0.w;
-        bool popNext = false, occluded = false;
-        int meta;
-        if (box) {
-            const size_t nd = 4 * (size_t)ref;
-            F4 q0 = fetch.node(nd), q1 = fetch.node(nd + 1), q2 = fetch.node(nd + 2), q3 = fetch.node(nd + 3);
-            const F4 s1 = st[slotsPerGroup + s];
-            const V3 invDir = v3(s1.x, s1.y, s1.z);
-            meta = __float_as_int(s1.w);
-            if (COUNT) cnt[MODE == kTraceMixed ? ((meta >> 12) & 3) : 0].nodes += 2;
-            int ref0 = f2i(q3.x), ref1 = f2i(q3.y), axis = f2i(q3.z);
-            const bool negX = invDir.x < 0, negY = invDir.y < 0, negZ = invDir.z < 0;
-            float t0 = 0, t1 = 0;
-            bool ok0 = slabPartialFlat(v3(q0.x, q0.y, q0.z), v3(q0.w, q1.x, q1.y), o, invDir, negX, negY, negZ, &t0);
-            bool ok1 = slabPartialFlat(v3(q1.z, q1.w, q2.x), v3(q2.y, q2.z, q2.w), o, invDir, negX, negY, negZ, &t1);
-            ok0 = ok0 & (ref0 != kEmptyRef);
-            ok1 = ok1 & (ref1 != kEmptyRef);
-            bool nearIs1 = axis == 0 ? negX : (axis == 1 ? negY : negZ);
-            int refNear = nearIs1 ? ref1 : ref0, refFar = nearIs1 ? ref0 : ref1;
-            bool okNear = nearIs1 ? ok1 : ok0, okFar = nearIs1 ? ok0 : ok1;
-            float tNear = nearIs1 ? t1 : t0, tFar = nearIs1 ? t0 : t1;
-            if (okFar) {
-                stack[k][meta & 255] = make_int2(refFar, __float_as_int(tFar));
-                ++meta;
-            }
-            if (okNear && tNear < tMax) ref = refNear;
-            else popNext = true;
-        } else {
-            const int slot = ~ref;
-            const size_t tp = 3 * (size_t)slot;
-            F4 a = fetch.tri(tp);
-            const F4 s2 = st[2 * slotsPerGroup + s];
-            meta = __float_as_int(st[slotsPerGroup + s].w);
-            const bool any = MODE == kTraceMixed ? ((meta >> 12) & 3) == 1 : MODE == kTraceAny;
-            int tag = f2i(a.w);
-            int type = tag & kTagTypeMask;
-            if (COUNT) cnt[MODE == kTraceMixed ? ((meta >> 12) & 3) : 0].prims += 1;
-            float t, b0 = 0, b1 = 0, b2 = 0;
-            bool h;
-            if (type == 0) {
-                F4 b = fetch.tri(tp + 1), c = fetch.tri(tp + 2);
-                Ray ray;  // the sheared test reads o and tMax only
-                ray.o = o;
-                ray.tMax = tMax;
-                ray.d = v3(0.f);
-                RayShear shear;
-                shear.kz = (meta >> 8) & 3;
-                shear.kx = shear.ky = 0;  // triangleTestSheared reads kz only (rotateToZ)
-                shear.Sx = s2.x, shear.Sy = s2.y, shear.Sz = s2.z;
-                h = triangleTestSheared(ray, shear, v3(a.x, a.y, a.z), v3(b.x, b.y, b.z), v3(c.x, c.y, c.z), &t, &b0, &b1, &b2);
-                if (!any && (tag & kTagDegenerate)) h = false;
-            } else {
-                Ray full;  // planes and spheres want the direction: it is only in the queue
-                source(__float_as_int(s2.w), &full);
-                full.tMax = tMax;
-                if (type == 1) h = aaplaneTest(full, bvh.planeParams + 48 * (size_t)(tag >> kTagShapeShift), &t, nullptr);
-                else h = sphereTestGuarded(full, bvh.sphereParams + 48 * (size_t)(tag >> kTagShapeShift), &t);
-            }
-            if (h) {
-                if (any) occluded = true;
-                else {
-                    tMax = t;
-                    st[s].w = t;
-                    st[3 * slotsPerGroup + s] = make_float4(__int_as_float(slot), b0, b1, b2);
-                }
-            }
-            if (occluded) ref = kEmptyRef;
-            else if (tag & kTagLast) popNext = true;
-            else ref = ~(slot + 1);
-        }
-        if (popNext) {
-            ref = kEmptyRef;
-            int sp = meta & 255;
-            while (sp > 0) {
-                --sp;
-                int2 e = stack[k][sp];
-                if (__int_as_float(e.y) < tMax) {
-                    ref = e.x;
-                    break;
-                }
-            }
-            meta = (meta & ~255) | sp;
-        }
-        if (box || popNext) st[slotsPerGroup + s].w = __int_as_float(meta);
-        if (ref == kEmptyRef) {
-            const int kind = MODE == kTraceMixed ? ((meta >> 12) & 3) : (MODE == kTraceAny ? 1 : 0);
-            const int idx = __float_as_int(st[2 * slotsPerGroup + s].w);
-            const F4 hq = st[3 * slotsPerGroup + s];
-            Hit hit;
-            hit.prim = __float_as_int(hq.x);
-            hit.t = tMax, hit.b0 = hq.y, hit.b1 = hq.z, hit.b2 = hq.w;
-            Ray ray;
-            ray.o = o, ray.d = v3(0.f), ray.tMax = tMax;
-            sink(idx, kind, ray, hit, kind == 1 ? occluded : hit.prim >= 0);
-        }
-        if (k) refB = ref;
-        else refA = ref;
-        }
-    }
-}
-
 template <int MODE, bool COUNT, class Source, class Sink>
 __device__ __forceinline__ void tracePersistent(const DevBVH &bvh, Source source, int n, int *next, int fetchThreshold,
                                                 int phaseBias, TraverseCounters *cnt, Sink sink) {
-#ifdef PG_TRACE_DUAL
-    tracePersistentDual<MODE, COUNT>(bvh, GlobalFetch{bvh.nodes, bvh.tris}, 0, source, n, next, fetchThreshold, phaseBias, cnt, sink);
-#else
     tracePersistentFrom<MODE, COUNT>(bvh, GlobalFetch{bvh.nodes, bvh.tris}, source, n, next, fetchThreshold, phaseBias, cnt, sink);
-#endif
 }
-// dynamic shared memory a kernel built on tracePersistent needs besides a staged scene
-#ifdef PG_TRACE_DUAL
-constexpr size_t kTraceStateSmem = dualStateBytes(128);
-#else
-constexpr size_t kTraceStateSmem = 0;
-#endif
 
 }  // namespace pg
 #endif  // __CUDACC__

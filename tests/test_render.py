@@ -340,12 +340,14 @@ def test_gpu_shards_add_up(pkg, gpu, golden):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("knob", ["PBRTGPU_SORT_HITS=0", "PBRTGPU_SHADE_BLOCK=1024", "PBRTGPU_SHADE_SYNC=0", "PBRTGPU_SHADE_LAMBERT=0",
-                                  "PBRTGPU_LAMBERT_BLOCK=2562"])
+@pytest.mark.parametrize("knob", ["PBRTGPU_SORT_HITS=0", "PBRTGPU_SORT_HITS=1", "PBRTGPU_SHADE_BLOCK=1024", "PBRTGPU_SHADE_SYNC=0",
+                                  "PBRTGPU_SHADE_LAMBERT=0", "PBRTGPU_LAMBERT_BLOCK=2562", "PBRTGPU_TRACE_SHARED_SCENE=0",
+                                  "PBRTGPU_FETCH_THRESHOLD=1", "PBRTGPU_FETCH_THRESHOLD=32"])
 def test_gpu_scheduling_knobs_do_not_change_the_image(pkg, gpu, monkeypatch, knob):
     """How vertices are mapped to threads -- the hit queue split by material class, the shade block shape, phase
     barriers or none -- must not change any path: only the order of float atomics into a film pixel may differ."""
-    hs = load_case(pkg, "box_glass")  # matte + plastic + glass: both material classes in one image
+    hs = load_case(pkg, "box_glass")  # matte + plastic + smooth and rough glass: all three material classes in one image (the
+    # default splits the hit queue into three runs and stages this small scene in shared memory; SORT_HITS=1: two runs)
     gpu.upload(hs)
     film, _ = gpu.render(hs.params)
     a = hs.film_to_rgb(film)

@@ -165,13 +165,18 @@ def reference_arm(args):
         "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
 
-def ncu_kernel_figures(kernel_substr):
+def ncu_kernel_figures(kernel_substr, workload_tag=None):
     """Lanes per instruction, issue rate and L2 hit rate of a kernel from the newest committed ncu summary under
     profiles/ (tools/ncu_summary.py over an `ncu --set full` capture of this same bench command): the average over
-    the captured launches of that kernel, weighted by their duration."""
+    the captured launches of that kernel, weighted by their duration.  workload_tag: only summaries whose file name
+    carries it (the C4 captures: *_c4_*), else only those that carry no workload tag (killeroo)."""
     import glob
     best = None
     for path in sorted(glob.glob(os.path.join(ROOT, "profiles", "*ncu*summary*.txt"))):
+        if workload_tag is None and "_c4_" in os.path.basename(path):
+            continue
+        if workload_tag is not None and ("_%s_" % workload_tag) not in os.path.basename(path):
+            continue
         blocks, cur, rec = [], None, {}
         for line in list(open(path)) + ["----"]:
             if line.startswith("----"):
@@ -501,14 +506,18 @@ def main():
         tj = json.load(open(tp))
         if tj.get("workload", "killeroo") == tag:
             traffic, traffic_src = tj["dram_bytes_read"] + tj["dram_bytes_write"], os.path.basename(tp) + ": " + tj["capture"]
+            # launches differ in size (first depth against last, one batch against another): carry the capture's DRAM bytes per
+            # millisecond over to this run's average launch
+            if tj.get("duration_ms") and tc["launches"] and tc["ms"] > 0:
+                traffic = traffic / tj["duration_ms"] * (tc["ms"] / tc["launches"])
     alg_per_launch = alg_bytes / max(1, tc["launches"])
-    ncu = ncu_kernel_figures("k_ptrace_fused") if tag == "killeroo" else None
+    ncu = ncu_kernel_figures("k_ptrace_fused", "c4" if tag == "c4" else None)
     # What bounds the kernel: on killeroo the BVH (9 MB) is served by L1 / L2 and DRAM sees 5 % of the algorithmic bytes --
     # the limiter is the SM's issue rate times the share of lanes that do work.  `achieved / peak / frac` stay the
     # HBM-normalised figures of SURVEY.md 8(d), the common yardstick; they are not a claim that the kernel is at 63 %
     # of a memory roofline.
     roofline = {"kernel": "k_ptrace_fused (+ k_ptrace_closest for the camera rays)",
-                "bound": "issue" if tag == "killeroo" else "hbm", "yardstick": "hbm (SURVEY.md 8(d) algorithmic bytes / measured copy bandwidth)",
+                "bound": "issue" if tag == "killeroo" else "hbm latency (L2 hit 59 %, 1.06 TB/s of 32-byte DRAM sectors under the launch: profiles/r02o_ncu_c4_trace_summary.txt)", "yardstick": "hbm (SURVEY.md 8(d) algorithmic bytes / measured copy bandwidth)",
                 "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 "issue_frac": ncu["issue"] if ncu else None, "lanes_per_inst": ncu["lanes"] if ncu else None,
                 "thread_inst_frac": (ncu["issue"] * ncu["lanes"] / 32.0) if ncu else None, "l2_hit": ncu.get("l2_hit") if ncu else None,

@@ -169,11 +169,11 @@ def ncu_kernel_figures(kernel_substr, workload_tag=None):
     """Lanes per instruction, issue rate and L2 hit rate of a kernel from the newest committed ncu summary under
     profiles/ (tools/ncu_summary.py over an `ncu --set full` capture of this same bench command): the average over
     the captured launches of that kernel, weighted by their duration.  workload_tag: only summaries whose file name
-    carries it (the C4 captures: *_c4_*), else only those that carry no workload tag (killeroo)."""
+    carries it (the C4 captures: *_c4_*; Cornell: *_c1_*), else only those that carry no workload tag (killeroo)."""
     import glob
     best = None
     for path in sorted(glob.glob(os.path.join(ROOT, "profiles", "*ncu*summary*.txt"))):
-        if workload_tag is None and "_c4_" in os.path.basename(path):
+        if workload_tag is None and any(t in os.path.basename(path) for t in ("_c4_", "_c1_")):
             continue
         if workload_tag is not None and ("_%s_" % workload_tag) not in os.path.basename(path):
             continue

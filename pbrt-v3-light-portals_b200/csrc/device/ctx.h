@@ -38,6 +38,7 @@ struct pbrtgpu_ctx {
     // Halton tables (uploaded at create)
     unsigned short *dPerms = nullptr;
     unsigned long long *dPrimeMagic = nullptr;
+    pg::HaltonDim *dHaltonDims = nullptr;  // per-dimension records of the Halton sampler (sampler.h)
     int *dPrimes = nullptr, *dPrimeSums = nullptr;  // first 1000 primes and their running sums
     // wavefront state of the path integrator (render.cu), grown on demand
     pg::DeviceBuffer wave[24];

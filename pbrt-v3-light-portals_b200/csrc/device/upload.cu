@@ -107,6 +107,10 @@ int pbrtgpu_create(int cuda_device, pbrtgpu_ctx **out) {
         std::vector<unsigned long long> magic = primeMagics(primes);
         if ((e = cudaMalloc((void **)&ctx->dPrimeMagic, magic.size() * 8)) != cudaSuccess) return bail(e, "cudaMalloc(primeMagic)");
         cudaMemcpy(ctx->dPrimeMagic, magic.data(), magic.size() * 8, cudaMemcpyHostToDevice);
+        std::vector<HaltonDim> dims(primes.size());
+        fillHaltonDims(primes.data(), sums.data(), perms.data(), (int)primes.size(), dims.data());
+        if ((e = cudaMalloc((void **)&ctx->dHaltonDims, dims.size() * sizeof(HaltonDim))) != cudaSuccess) return bail(e, "cudaMalloc(haltonDims)");
+        cudaMemcpy(ctx->dHaltonDims, dims.data(), dims.size() * sizeof(HaltonDim), cudaMemcpyHostToDevice);
     }
     *out = ctx;
     return PBRTGPU_OK;
@@ -124,6 +128,7 @@ void pbrtgpu_destroy(pbrtgpu_ctx *ctx) {
     if (ctx->dPrimes) cudaFree(ctx->dPrimes);
     if (ctx->dPrimeSums) cudaFree(ctx->dPrimeSums);
     if (ctx->dPrimeMagic) cudaFree(ctx->dPrimeMagic);
+    if (ctx->dHaltonDims) cudaFree(ctx->dHaltonDims);
     if (ctx->dTotals) cudaFree(ctx->dTotals);
     if (ctx->dFetch) cudaFree(ctx->dFetch);
     if (ctx->dTraversalCounts) cudaFree(ctx->dTraversalCounts);

@@ -115,7 +115,7 @@ PG_HD void stageShadePhased(const WaveParams &w, int depth, int cur, int pos, bo
     const int flagsNS = BSDF_ALL & ~BSDF_SPECULAR;
     // ---- phase 0: path state, the hit record -> SurfaceInteraction, emitted light (path.cpp:91-96)
     int slot = 0, prim = 0, flags = 0, bounces = 0, mat = -1;
-    bool specularBounce = false;
+    bool specularBounce = false, touchL = false;
     Ray ray, next;
     Spec L = spec(0.f), beta = spec(0.f);
     float wvl0 = 0, etaScale = 0;
@@ -125,12 +125,21 @@ PG_HD void stageShadePhased(const WaveParams &w, int depth, int cur, int pos, bo
         ray = loadRay(w.rays[cur], pos);
         F4 hit = w.hits[pos];
         prim = f2i(hit.x);
-        F4 Lq = w.L[slot], bq = w.beta[slot];
-        L = spec(Lq.x, Lq.y, Lq.z), beta = spec(bq.x, bq.y, bq.z);
-        wvl0 = Lq.w, etaScale = bq.w;
+        F4 bq = w.beta[slot];
+        beta = spec(bq.x, bq.y, bq.z);
+        etaScale = bq.w;
         flags = w.flags[slot];
         bounces = flags & 255;
         specularBounce = (flags >> 8) & 1;
+        // The path's radiance record {L, hero wavelength} is read and written back only by the vertices that need it: those
+        // that add emitted light (path.cpp:91-96) and, in scenes with a dispersive material, all of them (the wavelength).
+        // Everywhere else the 16-byte gather and the 16-byte scatter per vertex would move an unchanged value.
+        touchL = !w.skipWavelength || ((bounces == 0 || specularBounce) && w.sc.primLight && PG_LD(w.sc.primLight + prim) >= 0);
+        if (touchL) {
+            F4 Lq = w.L[slot];
+            L = spec(Lq.x, Lq.y, Lq.z);
+            wvl0 = Lq.w;
+        }
         it = hitInteraction(w.sc, prim, hit.y, hit.z, hit.w, ray);
         PG_TRACE("shade d=%d slot=%d prim=%d o=(%.9g %.9g %.9g) d=(%.9g %.9g %.9g) p=(%.9g %.9g %.9g) n=(%g %g %g) bounces=%d\n", depth, slot, prim, ray.o.x, ray.o.y, ray.o.z, ray.d.x, ray.d.y, ray.d.z, it.p.x, it.p.y, it.p.z, it.n.x, it.n.y, it.n.z, bounces);
         if (bounces == 0 || specularBounce) L += beta * hitLe(w.sc, prim, it.n, -ray.d);
@@ -301,7 +310,7 @@ PG_HD void stageShadePhased(const WaveParams &w, int depth, int cur, int pos, bo
         }
         w.dim[slot] = smp.dim;
     }
-    if (active) w.L[slot] = f4(L.r, L.g, L.b, wvl0);
+    if (active && touchL) w.L[slot] = f4(L.r, L.g, L.b, wvl0);
     if (alive) {
         w.beta[slot] = f4(beta.r, beta.g, beta.b, etaScale);
         w.flags[slot] = (flags & ~0x1ff) | bounces | (specularBounce ? 256 : 0);

@@ -39,7 +39,6 @@ struct pbrtgpu_ctx {
     unsigned short *dPerms = nullptr;
     unsigned long long *dPrimeMagic = nullptr;
     pg::HaltonDim *dHaltonDims = nullptr;  // per-dimension records of the Halton sampler (sampler.h)
-    unsigned short *dPerms2 = nullptr;     // ... and the digit-pair permutation tables of its small bases
     int *dPrimes = nullptr, *dPrimeSums = nullptr;  // first 1000 primes and their running sums
     // wavefront state of the path integrator (render.cu), grown on demand
     pg::DeviceBuffer wave[24];

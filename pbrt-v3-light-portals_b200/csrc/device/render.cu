@@ -379,7 +379,7 @@ extern "C" int pbrtgpu_halton_samples(pbrtgpu_ctx *ctx, const pbrtgpu_render_par
         if (dim[i] < 0 || dim[i] >= kPrimeTableSize) return ctx->fail(PBRTGPU_ERR_INVALID, "HaltonSampler can only sample %d dimensions.", kPrimeTableSize);
     PG_CUDA(ctx, cudaSetDevice(ctx->device));
     HaltonParams h = makeHaltonParams(params->sample_bounds, params->sample_at_pixel_center);
-    h.primes = ctx->dPrimes, h.primeSums = ctx->dPrimeSums, h.perms = ctx->dPerms, h.primeMagic = ctx->dPrimeMagic, h.dims = ctx->dHaltonDims, h.perms2 = ctx->dPerms2;
+    h.primes = ctx->dPrimes, h.primeSums = ctx->dPrimeSums, h.perms = ctx->dPerms, h.primeMagic = ctx->dPrimeMagic, h.dims = ctx->dHaltonDims;
     int rc;
     size_t bytes = (size_t)n * (8 + 8 + 4 + 4);
     if ((rc = ensureBuffer(ctx, ctx->scratch[2], bytes)) != PBRTGPU_OK) return rc;

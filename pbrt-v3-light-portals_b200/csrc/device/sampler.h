@@ -26,22 +26,12 @@ constexpr int kArrayStartDim = 5;  // GlobalSampler::arrayStartDim (sampler.h:12
 // its digit permutation starts, and the two per-base constants of ScrambledRadicalInverseSpecialized
 // (lowdiscrepancy.cpp:406-423) -- invBase = 1 / base and the tail invBase * perm[0] / (1 - invBase), both computed on the
 // host by the same correctly rounded float operations in the same order, so their bits are the device's.
-//
-// Bases below 256 (the first 54 dimensions: everything a path of up to five bounces draws) take their digits TWO AT A TIME:
-// a is divided by base^2 (magic2 / shift2, same construction and the same exactness argument: base^2 < 2^16 is not a power
-// of two and a < 2^31), and the pair d0 + base * d1 indexes a second table, perms2[perm2Offset + pair] = perm[d0] * base +
-// perm[d1] -- exactly what two rounds of `reversedDigits = reversedDigits * base + perm[digit]` add.  invBaseN is still
-// multiplied by invBase once per digit, in the same order.  The leading pair may be a single digit (pair < base): the
-// reference's loop stops at the most significant non-zero digit, so does this one.
 struct HaltonDim {
     unsigned base, magic32;
-    int shift;  // floor(log2 base) | floor(log2 base^2) << 8
-    int permOffset;
+    int shift, permOffset;
     float invBase, tail;
-    unsigned magic2;  // 0: no pair table for this base
-    int perm2Offset;
+    unsigned pad[2];
 };
-constexpr unsigned kHaltonPairBaseLimit = 256;
 
 struct HaltonParams {
     int baseScales[2], baseExponents[2];
@@ -55,7 +45,6 @@ struct HaltonParams {
     const unsigned long long *primeMagic;  // 2 x 1000 entries (halton_tables.h:primeMagics): 64-bit magics, then 32-bit ones
     const unsigned short *perms;   // 3,682,913 entries
     const HaltonDim *dims;         // 1000 entries (fillHaltonDims)
-    const unsigned short *perms2;  // pair tables of the bases below kHaltonPairBaseLimit (fillHaltonPairTables)
 };
 
 PG_HD int modPos(int a, int b) {  // Mod(), pbrt.h
@@ -155,34 +144,14 @@ PG_HD int floorLog2u(unsigned v) {
 #endif
 }
 // the short loop with the dimension's constants from its record
-PG_HD float scrambledRadicalInverseSmall(const HaltonDim &d, const unsigned short *perm, const unsigned short *perms2, unsigned a32) {
+PG_HD float scrambledRadicalInverseSmall(const HaltonDim &d, const unsigned short *perm, unsigned a32) {
     const unsigned base = d.base, magic32 = d.magic32;
-    const int s = d.shift & 255;
+    const int s = d.shift;
     const float invBase = d.invBase;
     unsigned long long reversedDigits = 0;
     float invBaseN = 1;
     unsigned rev = 0;
-    if (a32 && d.magic2) {
-        const unsigned b2 = base * base, magic2 = d.magic2;
-        const int s2 = d.shift >> 8;
-        const unsigned short *perm2 = perms2 + d.perm2Offset;
-        for (;;) {
-            unsigned next = mulhi32(a32, magic2) >> s2;
-            unsigned pair = a32 - next * b2;
-            invBaseN *= invBase;
-            if (next == 0) {
-                if (pair < base) reversedDigits = (unsigned long long)rev * base + PG_LD(perm + pair);  // one leading digit
-                else {
-                    invBaseN *= invBase;
-                    reversedDigits = (unsigned long long)rev * b2 + PG_LD(perm2 + pair);
-                }
-                break;
-            }
-            invBaseN *= invBase;
-            rev = rev * b2 + PG_LD(perm2 + pair);
-            a32 = next;
-        }
-    } else if (a32) {
+    if (a32) {
         for (;;) {
             unsigned next = mulhi32(a32, magic32) >> s;
             unsigned digit = a32 - next * base;
@@ -255,12 +224,10 @@ PG_NI_SAMPLER float haltonSample(const HaltonParams &h, long long index, int dim
         HaltonDim d;
         d.base = q0.x, d.magic32 = q0.y, d.shift = (int)q0.z, d.permOffset = (int)q0.w;
         d.invBase = __uint_as_float(q1.x), d.tail = __uint_as_float(q1.y);
-        const uint2 q2 = __ldg(reinterpret_cast<const uint2 *>(h.dims + dim) + 3);
-        d.magic2 = q2.x, d.perm2Offset = (int)q2.y;
 #else
         const HaltonDim d = h.dims[dim];
 #endif
-        return scrambledRadicalInverseSmall(d, h.perms + d.permOffset, h.perms2, (unsigned)index);
+        return scrambledRadicalInverseSmall(d, h.perms + d.permOffset, (unsigned)index);
     }
     unsigned base = (unsigned)PG_LD(h.primes + dim);
     return scrambledRadicalInverseBase(base, PG_LD(h.primeMagic + dim), (unsigned)PG_LD(h.primeMagic + kHaltonPrimes + dim),
@@ -312,7 +279,6 @@ inline HaltonParams makeHaltonParams(const int sampleBounds[4], int sampleAtPixe
     h.primeMagic = nullptr;
     h.perms = nullptr;
     h.dims = nullptr;
-    h.perms2 = nullptr;
     return h;
 }
 
@@ -329,29 +295,8 @@ inline void fillHaltonDims(const int *primes, const int *primeSums, const unsign
         const float invBase = (float)1 / (float)d.base;
         d.invBase = invBase;
         d.tail = invBase * (float)perms[primeSums[i]] / (1 - invBase);
-        d.magic2 = 0;
-        d.perm2Offset = 0;
+        d.pad[0] = d.pad[1] = 0;
     }
-}
-// The pair tables (see HaltonDim) of the leading dimensions whose base is below kHaltonPairBaseLimit; fills in magic2 / shift2 /
-// perm2Offset of their records and returns the entries written.  out = nullptr: only counts.
-inline size_t fillHaltonPairTables(const unsigned short *perms, int n, HaltonDim *dims, unsigned short *out) {
-    size_t total = 0;
-    for (int i = 0; i < n && dims[i].base < kHaltonPairBaseLimit; ++i) {
-        const unsigned base = dims[i].base, b2 = base * base;
-        if (out) {
-            const unsigned short *perm = perms + dims[i].permOffset;
-            for (unsigned d1 = 0; d1 < base; ++d1)
-                for (unsigned d0 = 0; d0 < base; ++d0) out[total + d0 + base * d1] = (unsigned short)(perm[d0] * base + perm[d1]);
-            int s2 = 0;
-            while ((2u << s2) <= b2) ++s2;
-            dims[i].shift |= s2 << 8;
-            dims[i].magic2 = (unsigned)(((1ull << (32 + s2)) + (unsigned long long)b2 - 1) / (unsigned long long)b2);
-            dims[i].perm2Offset = (int)total;
-        }
-        total += b2;
-    }
-    return total;
 }
 
 // The per-path view of GlobalSampler: interval sample index + running dimension.

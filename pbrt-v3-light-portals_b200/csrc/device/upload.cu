@@ -109,10 +109,6 @@ int pbrtgpu_create(int cuda_device, pbrtgpu_ctx **out) {
         cudaMemcpy(ctx->dPrimeMagic, magic.data(), magic.size() * 8, cudaMemcpyHostToDevice);
         std::vector<HaltonDim> dims(primes.size());
         fillHaltonDims(primes.data(), sums.data(), perms.data(), (int)primes.size(), dims.data());
-        std::vector<unsigned short> perms2(fillHaltonPairTables(perms.data(), (int)primes.size(), dims.data(), nullptr));
-        fillHaltonPairTables(perms.data(), (int)primes.size(), dims.data(), perms2.data());
-        if ((e = cudaMalloc((void **)&ctx->dPerms2, perms2.size() * sizeof(unsigned short))) != cudaSuccess) return bail(e, "cudaMalloc(perms2)");
-        cudaMemcpy(ctx->dPerms2, perms2.data(), perms2.size() * sizeof(unsigned short), cudaMemcpyHostToDevice);
         if ((e = cudaMalloc((void **)&ctx->dHaltonDims, dims.size() * sizeof(HaltonDim))) != cudaSuccess) return bail(e, "cudaMalloc(haltonDims)");
         cudaMemcpy(ctx->dHaltonDims, dims.data(), dims.size() * sizeof(HaltonDim), cudaMemcpyHostToDevice);
     }
@@ -133,7 +129,6 @@ void pbrtgpu_destroy(pbrtgpu_ctx *ctx) {
     if (ctx->dPrimeSums) cudaFree(ctx->dPrimeSums);
     if (ctx->dPrimeMagic) cudaFree(ctx->dPrimeMagic);
     if (ctx->dHaltonDims) cudaFree(ctx->dHaltonDims);
-    if (ctx->dPerms2) cudaFree(ctx->dPerms2);
     if (ctx->dTotals) cudaFree(ctx->dTotals);
     if (ctx->dFetch) cudaFree(ctx->dFetch);
     if (ctx->dTraversalCounts) cudaFree(ctx->dTraversalCounts);

@@ -154,10 +154,7 @@ extern "C" int hostsim_render(void *p, const pbrtgpu_render_params *rp, float *f
     w.hal.primes = primes.data(), w.hal.primeSums = sums.data(), w.hal.perms = perms.data(), w.hal.primeMagic = magic.data();
     std::vector<HaltonDim> haltonDims(primes.size());
     fillHaltonDims(primes.data(), sums.data(), perms.data(), (int)primes.size(), haltonDims.data());
-    std::vector<unsigned short> perms2(fillHaltonPairTables(perms.data(), (int)primes.size(), haltonDims.data(), nullptr));
-    fillHaltonPairTables(perms.data(), (int)primes.size(), haltonDims.data(), perms2.data());
     w.hal.dims = haltonDims.data();
-    w.hal.perms2 = perms2.data();
     bool dispersiveTrans = false;
     const bool tree = rp->integrator == PBRTGPU_INTEGRATOR_DIRECT && rp->max_depth > 1 &&
                       maxSpecularTransmissionLobes(matLobes, s->n_materials, &dispersiveTrans) > 0;
@@ -307,15 +304,11 @@ extern "C" int hostsim_halton(const pbrtgpu_render_params *rp, const int32_t *xy
     HaltonParams h = makeHaltonParams(rp->sample_bounds, rp->sample_at_pixel_center);
     h.primes = primes.data(), h.primeSums = sums.data(), h.perms = perms.data(), h.primeMagic = magic.data();
     static std::vector<HaltonDim> haltonDims;
-    static std::vector<unsigned short> perms2;
     if (haltonDims.empty()) {
         haltonDims.resize(primes.size());
         fillHaltonDims(primes.data(), sums.data(), perms.data(), (int)primes.size(), haltonDims.data());
-        perms2.resize(fillHaltonPairTables(perms.data(), (int)primes.size(), haltonDims.data(), nullptr));
-        fillHaltonPairTables(perms.data(), (int)primes.size(), haltonDims.data(), perms2.data());
     }
     h.dims = haltonDims.data();
-    h.perms2 = perms2.data();
     for (int64_t i = 0; i < n; ++i)
         out[i] = haltonSample(h, haltonPixelOffset(h, xy[2 * i], xy[2 * i + 1]) + num[i] * h.sampleStride, dim[i]);
     return 0;

@@ -1,7 +1,7 @@
-"""Turn the ncu outputs of tools/profile_r02r.sh into the two small files the bench line cites.
+"""Turn the ncu outputs of tools/profile_r02x.sh into the two small files the bench line cites.
 
-    python tools/ncu_postprocess.py shares  gpurun_out/r02r_launches.csv        > profiles/r02r_launch_shares.csv
-    python tools/ncu_postprocess.py traffic gpurun_out/r02r_ncu_bench_step_raw.csv k_ptrace_fused > profiles/r02r_traffic.json
+    python tools/ncu_postprocess.py shares  gpurun_out/r02x_launches.csv        > profiles/r02x_launch_shares.csv
+    python tools/ncu_postprocess.py traffic gpurun_out/r02x_ncu_bench_step_raw.csv k_ptrace_fused > profiles/r02x_traffic.json
 """
 import csv, io, json, re, sys
 

@@ -46,9 +46,15 @@ __global__ void __launch_bounds__(kTraceBlock) k_intersect_any(DevScene sc, cons
 }
 
 // Persistent variants (trace_persistent.h); `rays` / outputs already offset to the chunk, n < 2^31.
+// COUNT (profile mode, pbrtgpu_set_profile): box tests and primitive tests of the batch are added to counts[0], counts[1] --
+// what tests/test_rays.py compares with the tallies of the reference's own loop (the same nodes entered, the same primitives
+// tested: "same visiting order" checked, not argued).
+template <bool COUNT>
 __global__ void __launch_bounds__(kTraceBlock, kPersistMinBlocks) k_pintersect_closest(DevScene sc, const float4 *__restrict__ rays, int n,
-                                                                    float4 *__restrict__ hits, int *next, int fetchThreshold, int phaseBias) {
-    tracePersistent<kTraceClosest, false>(sc.bvh, SingleQueue{rays, 0}, n, next, fetchThreshold, phaseBias, nullptr, [&](int i, int, const Ray &ray, const Hit &h, bool found) {
+                                                                    float4 *__restrict__ hits, int *next, int fetchThreshold, int phaseBias,
+                                                                    unsigned long long *counts) {
+    TraverseCounters c = {0, 0};
+    tracePersistent<kTraceClosest, COUNT>(sc.bvh, SingleQueue{rays, 0}, n, next, fetchThreshold, phaseBias, &c, [&](int i, int, const Ray &ray, const Hit &h, bool found) {
         float4 out;
         out.x = __int_as_float(found ? __ldg(sc.primOrigId + h.prim) : -1);
         out.y = ray.tMax;
@@ -56,12 +62,23 @@ __global__ void __launch_bounds__(kTraceBlock, kPersistMinBlocks) k_pintersect_c
         out.w = found ? h.b1 : 0.f;
         hits[i] = out;
     });
+    if (COUNT) {
+        atomicAdd(counts, (unsigned long long)c.nodes);
+        atomicAdd(counts + 1, (unsigned long long)c.prims);
+    }
 }
 
+template <bool COUNT>
 __global__ void __launch_bounds__(kTraceBlock, kPersistMinBlocks) k_pintersect_any(DevScene sc, const float4 *__restrict__ rays, int n,
-                                                                unsigned char *__restrict__ occluded, int *next, int fetchThreshold, int phaseBias) {
-    tracePersistent<kTraceAny, false>(sc.bvh, SingleQueue{rays, 1}, n, next, fetchThreshold, phaseBias, nullptr,
+                                                                unsigned char *__restrict__ occluded, int *next, int fetchThreshold, int phaseBias,
+                                                                unsigned long long *counts) {
+    TraverseCounters c = {0, 0};
+    tracePersistent<kTraceAny, COUNT>(sc.bvh, SingleQueue{rays, 1}, n, next, fetchThreshold, phaseBias, &c,
                                       [&](int i, int, const Ray &, const Hit &, bool occ) { occluded[i] = occ ? 1 : 0; });
+    if (COUNT) {
+        atomicAdd(counts, (unsigned long long)c.nodes);
+        atomicAdd(counts + 1, (unsigned long long)c.prims);
+    }
 }
 
 int traceGrid(const pbrtgpu_ctx *ctx, long long n) {
@@ -87,12 +104,19 @@ static int timedLaunch(pbrtgpu_ctx *ctx, bool any, const void *dRays, long long 
             int m = (int)std::min(kChunk, n - off);
             long long blocks = std::min<long long>(((long long)m + kTraceBlock - 1) / kTraceBlock, (long long)ctx->smCount * ctx->persistBlocksPerSM);
             PG_CUDA(ctx, cudaMemsetAsync(ctx->dFetch, 0, sizeof(int), ctx->stream));
-            if (any)
-                k_pintersect_any<<<(int)blocks, kTraceBlock, 0, ctx->stream>>>(ctx->scene, (const float4 *)dRays + 2 * off, m,
-                                                                               (unsigned char *)dOut + off, ctx->dFetch, ctx->fetchThreshold, ctx->phaseBias);
+            const bool count = ctx->profile && ctx->dTraversalCounts;  // {closest, shadow, nee} x {node tests, prim tests}
+            if (any && count)
+                k_pintersect_any<true><<<(int)blocks, kTraceBlock, 0, ctx->stream>>>(ctx->scene, (const float4 *)dRays + 2 * off, m, (unsigned char *)dOut + off,
+                                                                                     ctx->dFetch, ctx->fetchThreshold, ctx->phaseBias, ctx->dTraversalCounts + 2);
+            else if (any)
+                k_pintersect_any<false><<<(int)blocks, kTraceBlock, 0, ctx->stream>>>(ctx->scene, (const float4 *)dRays + 2 * off, m, (unsigned char *)dOut + off,
+                                                                                      ctx->dFetch, ctx->fetchThreshold, ctx->phaseBias, nullptr);
+            else if (count)
+                k_pintersect_closest<true><<<(int)blocks, kTraceBlock, 0, ctx->stream>>>(ctx->scene, (const float4 *)dRays + 2 * off, m, (float4 *)dOut + off,
+                                                                                         ctx->dFetch, ctx->fetchThreshold, ctx->phaseBias, ctx->dTraversalCounts);
             else
-                k_pintersect_closest<<<(int)blocks, kTraceBlock, 0, ctx->stream>>>(ctx->scene, (const float4 *)dRays + 2 * off, m,
-                                                                                   (float4 *)dOut + off, ctx->dFetch, ctx->fetchThreshold, ctx->phaseBias);
+                k_pintersect_closest<false><<<(int)blocks, kTraceBlock, 0, ctx->stream>>>(ctx->scene, (const float4 *)dRays + 2 * off, m, (float4 *)dOut + off,
+                                                                                          ctx->dFetch, ctx->fetchThreshold, ctx->phaseBias, nullptr);
         }
     } else {
         int grid = traceGrid(ctx, n);

@@ -173,6 +173,40 @@ def test_gpu_killeroo_matches_oracle(pkg, gpu, oracle_lib):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("scene", ["soup", "killeroo"])
+def test_gpu_traversal_enters_the_nodes_the_reference_enters(pkg, soup, gpu, oracle_lib, scene):
+    """The visiting-order claim of bvh.h / trace_persistent.h, counted instead of argued: over a batch of closest-hit rays the
+    persistent kernel tests exactly the primitives the reference's loop (bvh.cpp:662-738, restated in oracle/port) tests, and
+    enters exactly the interior nodes it enters.  The reference counts one bounds test per node it visits (1 + 2 per interior
+    node whose bounds it passes); the device tests both children when it enters a record, record 0 -- the synthetic parent of
+    the root -- included: 2 + 2 per interior node, i.e. one more per ray.  A cull that differed, a child visited in the other
+    order (a different tMax at the far child's pop) or a leaf walked twice would move one of the two tallies.  Any-hit rays stop
+    at the first accepted primitive, with stacked entries left whose tMax-independent half the device has already tested, so
+    only the primitive tally is compared there."""
+    hs = soup if scene == "soup" else pkg.HostScene(scene_path("killeroo-path.pbrt"))
+    gpu.upload(hs)
+    lo, hi = ([-10, -10, -10], [10, 10, 10]) if scene == "soup" else ([-100, -100, -150], [100, 150, 50])
+    rays = np.concatenate([util.rays_incoherent_closest(hs.view, 300000, seed=21), util.rays_toward_box(300000, lo, hi, seed=22),
+                           util.rays_edge_cases(hs.view, 50000, seed=23)])
+    gpu.set_profile(True)
+    try:
+        ids, t, _ = gpu.intersect_closest(rays)
+        closest = gpu.get_profile()["trace_closest"]
+        srays = util.rays_shadow(hs.view, 300000, seed=24)
+        occ = gpu.intersect_any(srays)
+        shadow = gpu.get_profile()["trace_shadow"]
+    finally:
+        gpu.set_profile(False)
+    oid, ot, _, (nodes, prims) = util.oracle_closest(oracle_lib, hs.view, rays)
+    assert np.array_equal(ids, oid) and np.array_equal(util.bits(t), util.bits(ot))
+    assert closest["prim_tests"] == prims
+    assert closest["node_tests"] == nodes + len(rays)
+    oocc, (_, sprims) = util.oracle_any(oracle_lib, hs.view, srays)
+    assert np.array_equal(occ, oocc)
+    assert shadow["prim_tests"] == sprims
+
+
+@pytest.mark.gpu
 def test_gpu_edge_inputs(soup, gpu):
     gpu.upload(soup)
     ids, t, _ = gpu.intersect_closest(np.zeros((0, 8), np.float32))

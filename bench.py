@@ -472,12 +472,13 @@ def main():
     e2e_value = samples_per_step * e2e_steps / float(t_e2e.item()) / 1e6
     e2e_sync_value, e2e_pipeline = None, None
 
-    # ---- e2e as a renderer would run it (N = 1): TWO steps in flight.  Two contexts (each with its own copy of the scene, its
-    # own wave buffers and stream) take the steps in turn through the same three calls -- pbrtgpu_upload_scene from host
-    # memory, pbrtgpu_render_device_into, a film download into pinned memory -- so the scene upload of step k + 1 and the film
-    # download of step k - 1 run under the kernels of step k, and the tail of one step's launches is filled by the other's.
-    # Every step's H2D and D2H stay inside the timed region.  The one-step-at-a-time figure above is kept as `sync_value`.
-    if world == 1:
+    # ---- e2e as a renderer would run it: TWO steps in flight.  Two contexts (each with its own copy of the scene, its own
+    # wave buffers and stream) take the steps in turn through the same calls -- pbrtgpu_upload_scene from host memory,
+    # pbrtgpu_render_device_into, at N > 1 the NCCL reduce of the film, the film download into pinned memory (rank 0 at N > 1)
+    # -- so the scene upload of step k + 1 and the reduce / download of step k - 1 run under the kernels of step k, and the
+    # tail of one step's launches is filled by the other's.  Every step's H2D and D2H stay inside the timed region.  The
+    # one-step-at-a-time figure above is kept as `sync_value`.  PBRTGPU_BENCH_E2E_PIPELINE=0 skips this.
+    if os.environ.get("PBRTGPU_BENCH_E2E_PIPELINE", "1") != "0":
         ctx_b = pk.GpuContext(local)
         ctx_b.upload(hs)
         lanes = [(ctx, torch.cuda.Stream()), (ctx_b, torch.cuda.Stream())]
@@ -494,7 +495,10 @@ def main():
             c.upload(hs)
             c.render_device_into(params, film_t[i].data_ptr())
             with torch.cuda.stream(st):
-                host_films[i].view(-1).copy_(film_t[i], non_blocking=True)
+                if world > 1:
+                    dist.reduce(film_t[i], 0, async_op=True).wait()  # NCCL's stream behind the render, this stream behind NCCL
+                if rank == 0:
+                    host_films[i].view(-1).copy_(film_t[i], non_blocking=True)
                 done[i].record(st)
 
         for i in range(2):
@@ -502,26 +506,39 @@ def main():
         for k in range(2):  # warm-up: the second context's buffers, both lanes primed
             pipe_step(k)
         torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
         n_pipe = 2 * e2e_steps
         t0 = time.perf_counter()
         for k in range(n_pipe):
             pipe_step(k)
         torch.cuda.synchronize()
-        t_pipe = time.perf_counter() - t0
+        t_pipe = torch.tensor([time.perf_counter() - t0], device="cuda", dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t_pipe, op=dist.ReduceOp.MAX)
+        t_pipe = float(t_pipe.item())
         e2e_sync_value = e2e_value
         e2e_value = samples_per_step * n_pipe / t_pipe / 1e6
         ctx_b.close()
         ctx.set_stream(stream.cuda_stream)
         ctx.upload(hs)
-        # what the pipeline delivered for its last step against a one-step-at-a-time render of the same sample numbers
+        # what the pipeline delivered for its last step against a one-step-at-a-time render (and reduce) of the same sample numbers
         last = host_films[(n_pipe - 1) % 2].clone()
         set_range(n_pipe - 1)
-        ctx.render(params, out=film_host)
-        a, b = last.double().view(-1, 4), film_host_t.double().view(-1, 4)
-        pipe_rel = float(torch.sqrt(((a[:, :3] - b[:, :3]) ** 2).mean()) / b[:, :3].abs().mean())
-        e2e_pipeline = {"how": "two steps in flight: two contexts (own scene copy, wave buffers and stream), taking the steps in turn",
-                        "steps": n_pipe, "wall_ms": round(t_pipe * 1e3, 1),
-                        "film_rel_rmse_vs_synchronous_render": pipe_rel, "ok": bool(pipe_rel <= 1e-6 and torch.equal(a[:, 3], b[:, 3]))}
+        if world == 1:
+            ctx.render(params, out=film_host)
+        else:
+            ctx.render_device_into(params, film_t[0].data_ptr())
+            dist.reduce(film_t[0], 0)
+            if rank == 0:
+                film_host_t.view(-1).copy_(film_t[0])
+            torch.cuda.synchronize()
+        if rank == 0:
+            a, b = last.double().view(-1, 4), film_host_t.double().view(-1, 4)
+            pipe_rel = float(torch.sqrt(((a[:, :3] - b[:, :3]) ** 2).mean()) / b[:, :3].abs().mean())
+            e2e_pipeline = {"how": "two steps in flight: two contexts (own scene copy, wave buffers and stream), taking the steps in turn",
+                            "steps": n_pipe, "wall_ms": round(t_pipe * 1e3, 1),
+                            "film_rel_rmse_vs_synchronous_render": pipe_rel, "ok": bool(pipe_rel <= 1e-6 and torch.equal(a[:, 3], b[:, 3]))}
 
     if rank != 0:
         if world > 1:
